@@ -1,0 +1,213 @@
+"""ctypes binding of libgt4py_b200.so (the C ABI declared in include/gt4py_b200.h).
+
+The library is the only compute path of this package: if it cannot be loaded an ImportError-like
+RuntimeError is raised on first use -- there is no CPU or PyTorch fallback.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import POINTER, Structure, byref, c_char_p, c_double, c_float, c_int, c_int32, c_int64, c_size_t, c_uint32, c_void_p
+
+import numpy as np
+
+MAX_DIMS = 5
+
+OK, EINVAL, ECUDA, EUNSUP, ENOMEM = 0, -1, -2, -3, -4
+
+# dtype codes of include/gt4py_b200.h
+DTYPE_CODES = {
+    np.dtype("bool"): 1,
+    np.dtype("int8"): 2,
+    np.dtype("int16"): 3,
+    np.dtype("int32"): 4,
+    np.dtype("int64"): 5,
+    np.dtype("float32"): 6,
+    np.dtype("float64"): 7,
+}
+
+
+class B200Error(RuntimeError):
+    """A C-ABI call returned a negative status."""
+
+    def __init__(self, code: int, message: str):
+        super().__init__(f"libgt4py_b200 error {code}: {message}")
+        self.code = code
+
+
+class Field(Structure):
+    """struct b200_field"""
+
+    _fields_ = [
+        ("ptr", c_void_p),
+        ("stride", c_int64 * MAX_DIMS),
+        ("shape", c_int64 * MAX_DIMS),
+        ("origin", c_int32 * MAX_DIMS),
+        ("ndim", c_int32),
+        ("dtype", c_int32),
+    ]
+
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_PKG, "lib", "libgt4py_b200.so")
+_lib = None
+
+_VP = c_void_p
+_PROTOTYPES = {
+    "b200_abi_version": ([], c_int),
+    "b200_last_error": ([], c_char_p),
+    "b200_device_count": ([POINTER(c_int)], c_int),
+    "b200_set_device": ([c_int], c_int),
+    "b200_get_device": ([POINTER(c_int)], c_int),
+    "b200_device_sync": ([], c_int),
+    "b200_device_props": ([POINTER(c_int64)], c_int),
+    "b200_malloc": ([POINTER(_VP), c_size_t], c_int),
+    "b200_free": ([_VP], c_int),
+    "b200_host_alloc": ([POINTER(_VP), c_size_t], c_int),
+    "b200_host_free": ([_VP], c_int),
+    "b200_memcpy_h2d": ([_VP, _VP, c_size_t, _VP], c_int),
+    "b200_memcpy_d2h": ([_VP, _VP, c_size_t, _VP], c_int),
+    "b200_memcpy_d2d": ([_VP, _VP, c_size_t, _VP], c_int),
+    "b200_memset": ([_VP, c_int, c_size_t, _VP], c_int),
+    "b200_stream_create": ([POINTER(_VP)], c_int),
+    "b200_stream_destroy": ([_VP], c_int),
+    "b200_stream_sync": ([_VP], c_int),
+    "b200_event_create": ([POINTER(_VP)], c_int),
+    "b200_event_destroy": ([_VP], c_int),
+    "b200_event_record": ([_VP, _VP], c_int),
+    "b200_event_sync": ([_VP], c_int),
+    "b200_event_elapsed_ms": ([_VP, _VP, POINTER(c_float)], c_int),
+    "b200_stream_wait_event": ([_VP, _VP], c_int),
+    "b200_hdiff": ([POINTER(Field), POINTER(Field), POINTER(Field), POINTER(c_int64), c_int, c_int, _VP], c_int),
+    "b200_vadv": ([POINTER(Field)] * 5 + [c_double, POINTER(c_int64), c_int, _VP], c_int),
+    "b200_tridiag": ([POINTER(Field)] * 5 + [POINTER(c_int64), c_int, _VP], c_int),
+    "b200_module_load": ([_VP, c_size_t, POINTER(_VP)], c_int),
+    "b200_module_unload": ([_VP], c_int),
+    "b200_module_get_kernel": ([_VP, c_char_p, POINTER(_VP)], c_int),
+    "b200_kernel_set_smem": ([_VP, c_int], c_int),
+    "b200_launch": ([_VP, POINTER(c_uint32), POINTER(c_uint32), c_uint32, _VP, POINTER(_VP), c_int], c_int),
+}
+
+
+def declared_symbols():
+    """Every function include/gt4py_b200.h declares (kept in sync by tests/test_abi.py)."""
+    return sorted(_PROTOTYPES)
+
+
+def lib():
+    """Load (building first if the sources are newer) and return the ctypes library."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH) or os.environ.get("GT4PY_B200_REBUILD"):
+            from . import build as _build
+
+            _build.build()
+        try:
+            handle = ctypes.CDLL(LIB_PATH)
+        except OSError as exc:  # pragma: no cover
+            raise RuntimeError(
+                f"gt4py_b200: cannot load {LIB_PATH} ({exc}); run `python -m gt4py_b200.build`. "
+                "There is no fallback compute path."
+            ) from exc
+        for name, (argtypes, restype) in _PROTOTYPES.items():
+            fn = getattr(handle, name)
+            fn.argtypes = argtypes
+            fn.restype = restype
+        if handle.b200_abi_version() != 1:
+            raise RuntimeError("gt4py_b200: ABI version mismatch between Python host and library")
+        _lib = handle
+    return _lib
+
+
+def check(code: int):
+    if code != 0:
+        msg = lib().b200_last_error()
+        raise B200Error(code, msg.decode("utf-8", "replace") if msg else "")
+
+
+def device_count() -> int:
+    n = c_int(0)
+    try:
+        check(lib().b200_device_count(byref(n)))
+    except B200Error:
+        return 0
+    return n.value
+
+
+def device_props() -> dict:
+    arr = (c_int64 * 8)()
+    check(lib().b200_device_props(arr))
+    return {"sm_count": arr[0], "max_smem_optin": arr[1], "l2_bytes": arr[2],
+            "cc": (arr[3], arr[4]), "global_mem_mib": arr[5]}
+
+
+def synchronize():
+    check(lib().b200_device_sync())
+
+
+def set_device(dev: int):
+    check(lib().b200_set_device(int(dev)))
+
+
+class Stream:
+    """A non-blocking CUDA stream owned by the library."""
+
+    def __init__(self):
+        h = _VP()
+        check(lib().b200_stream_create(byref(h)))
+        self.handle = h
+
+    def synchronize(self):
+        check(lib().b200_stream_sync(self.handle))
+
+    def wait_event(self, event: "Event"):
+        check(lib().b200_stream_wait_event(self.handle, event.handle))
+
+    def __del__(self):
+        try:
+            if self.handle:
+                lib().b200_stream_destroy(self.handle)
+        except Exception:
+            pass
+
+
+class Event:
+    def __init__(self):
+        h = _VP()
+        check(lib().b200_event_create(byref(h)))
+        self.handle = h
+
+    def record(self, stream=None):
+        check(lib().b200_event_record(self.handle, stream_handle(stream)))
+
+    def synchronize(self):
+        check(lib().b200_event_sync(self.handle))
+
+    def elapsed_ms(self, stop: "Event") -> float:
+        ms = c_float(0.0)
+        check(lib().b200_event_elapsed_ms(self.handle, stop.handle, byref(ms)))
+        return ms.value
+
+    def __del__(self):
+        try:
+            if self.handle:
+                lib().b200_event_destroy(self.handle)
+        except Exception:
+            pass
+
+
+def stream_handle(stream) -> c_void_p:
+    """Accept None (legacy default stream), a Stream, an int handle, or an object with .cuda_stream
+    (e.g. torch.cuda.Stream) / .ptr (cupy)."""
+    if stream is None:
+        return _VP(None)
+    if isinstance(stream, Stream):
+        return stream.handle
+    if isinstance(stream, _VP):
+        return stream
+    if isinstance(stream, int):
+        return _VP(stream)
+    for attr in ("cuda_stream", "ptr", "handle"):
+        if hasattr(stream, attr):
+            return _VP(int(getattr(stream, attr)))
+    raise TypeError(f"cannot interpret {stream!r} as a CUDA stream")

@@ -1,0 +1,229 @@
+// hdiff.cu -- horizontal diffusion (lap-of-lap with optional flux limiter), hand-written for sm_100a.
+//
+// Reference semantics: tests/cartesian_tests/integration_tests/multi_feature_tests/
+// stencil_definitions.py:316-328 (limiter) and :206-216 (no limiter) of the reference.  Operator
+// association is kept exactly as written there and the file is compiled with -fmad=false, so the
+// results are bit-identical to the reference numpy backend (which evaluates node by node).
+//
+// Kernels
+//   hdiff_point   : one thread per grid point, any strides/alignment (variant 1, the safe path).
+//   hdiff_jmarch  : the HBM-bound path (variant 2).  A warp owns 64 consecutive I columns (two per
+//                   lane, 128-bit loads), marches along J keeping a 3-row rolling window of
+//                   in_field and 2 rows of the Laplacian in registers, and exchanges the I+-1
+//                   neighbours with warp shuffles.  Every in_field element is loaded once per
+//                   J-strip; the 4 overlap columns/rows between neighbouring warps/strips are L1/L2
+//                   hits, so DRAM traffic stays at ~24 B/point (8 in + 8 coeff + 8 out).
+#include "common.cuh"
+
+namespace b200 {
+
+// ------------------------------------------------------------------------------------------------
+// generic point kernel
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ double lap_pt(const double *__restrict__ in, int64_t si, int64_t sj)
+{
+    return 4.0 * in[0] - (((in[si] + in[-si]) + in[sj]) + in[-sj]);
+}
+
+template <bool LIMITER>
+__device__ __forceinline__ double limit(double res, double d)
+{
+    if (LIMITER) return (res * d > 0.0) ? 0.0 : res;
+    return res;
+}
+
+template <bool LIMITER>
+__global__ void __launch_bounds__(256)
+hdiff_point(View3<const double> in, View3<double> out, View3<const double> coeff, int ni, int nj,
+            int nk)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    int j = blockIdx.y * blockDim.y + threadIdx.y;
+    int k = blockIdx.z;
+    if (i >= ni || j >= nj || k >= nk) return;
+    const double *p = in.p + i * in.si + j * in.sj + k * in.sk;
+    const int64_t si = in.si, sj = in.sj;
+    double l0 = lap_pt(p, si, sj);
+    double lxp = lap_pt(p + si, si, sj), lxm = lap_pt(p - si, si, sj);
+    double lyp = lap_pt(p + sj, si, sj), lym = lap_pt(p - sj, si, sj);
+    double flx = limit<LIMITER>(lxp - l0, p[si] - p[0]);
+    double flxm = limit<LIMITER>(l0 - lxm, p[0] - p[-si]);
+    double fly = limit<LIMITER>(lyp - l0, p[sj] - p[0]);
+    double flym = limit<LIMITER>(l0 - lym, p[0] - p[-sj]);
+    double c = coeff.p[i * coeff.si + j * coeff.sj + k * coeff.sk];
+    out.p[i * out.si + j * out.sj + k * out.sk] = p[0] - c * (((flx - flxm) + fly) - flym);
+}
+
+// ------------------------------------------------------------------------------------------------
+// J-marching register kernel
+// ------------------------------------------------------------------------------------------------
+constexpr int JM_COLS_PER_WARP = 60;  // 64 loaded, 60 produced (lanes 1..30)
+
+// Load columns (col, col+1) of one row; columns outside [-2, ni+2) read as 0 (never used for a
+// stored result).  `row` points at column 0 of the row.
+__device__ __forceinline__ double2 load_pair(const double *__restrict__ row, int col, int ni)
+{
+    double2 v = make_double2(0.0, 0.0);
+    if (col >= -2) {
+        if (col + 1 < ni + 2) {
+            v = __ldg(reinterpret_cast<const double2 *>(row + col));
+        } else if (col < ni + 2) {
+            v.x = __ldg(row + col);
+        }
+    }
+    return v;
+}
+
+template <bool LIMITER, int PF>
+__global__ void __launch_bounds__(256)
+hdiff_jmarch(View3<const double> in, View3<double> out, View3<const double> coeff, int ni, int nj,
+             int nk, int tj)
+{
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const int wpb = blockDim.x >> 5;
+    const int col = (blockIdx.x * wpb + warp) * JM_COLS_PER_WARP - 2 + 2 * lane;
+    const int j0 = blockIdx.y * tj;
+    const int k = blockIdx.z;
+    if (col - 2 * lane + 2 >= ni) return;  // first produced column >= ni: whole warp idle (uniform)
+    const int jend = min(j0 + tj, nj);  // exclusive end of output rows
+    const int jmax = nj + 2;            // exclusive end of readable rows
+
+    const double *__restrict__ pin = in.p + (int64_t)k * in.sk;
+    const double *__restrict__ pco = coeff.p + (int64_t)k * coeff.sk;
+    double *__restrict__ pout = out.p + (int64_t)k * out.sk;
+    const int64_t sj = in.sj;
+
+    const bool store_x = lane >= 1 && lane <= 30 && col < ni;
+    const bool store_y = lane >= 1 && lane <= 30 && col + 1 < ni;
+
+    auto load_in = [&](int r) -> double2 {
+        return (r < jmax) ? load_pair(pin + (int64_t)r * sj, col, ni) : make_double2(0.0, 0.0);
+    };
+    auto load_co = [&](int r) -> double2 {
+        double2 v = make_double2(0.0, 0.0);
+        if (r >= j0 && r < jend) {
+            const double *row = pco + (int64_t)r * coeff.sj;
+            if (store_y) v = __ldcs(reinterpret_cast<const double2 *>(row + col));
+            else if (store_x) v.x = __ldcs(row + col);
+        }
+        return v;
+    };
+
+    // rolling window
+    double2 in0 = load_in(j0 - 2);
+    double2 in1 = load_in(j0 - 1);
+    double2 nin[PF], nco[PF];  // prefetch queues: rows jr+2 .. jr+1+PF of in, rows jr .. of coeff
+#pragma unroll
+    for (int u = 0; u < PF; ++u) {
+        nin[u] = load_in(j0 + u);
+        nco[u] = load_co(j0 - 2 + u);
+    }
+    double2 lap0 = make_double2(0.0, 0.0), flym1 = make_double2(0.0, 0.0);
+    double r0 = 0.0, lapr0 = 0.0;  // in(b+1, row jr) and lap(b+1, row jr)
+
+    for (int jb = j0 - 2; jb < jend; jb += PF) {
+#pragma unroll
+        for (int u = 0; u < PF; ++u) {
+            const int jr = jb + u;  // the row whose output is produced in this step
+            double2 in2 = nin[u];
+            double2 co = nco[u];
+            nin[u] = load_in(jr + 2 + PF);
+            nco[u] = load_co(jr + PF);
+            // Laplacian of row jr+1 on the own two columns
+            double l1 = __shfl_up_sync(0xffffffffu, in1.y, 1);    // in(a-1, jr+1)
+            double r1 = __shfl_down_sync(0xffffffffu, in1.x, 1);  // in(b+1, jr+1)
+            double2 lap1;
+            lap1.x = 4.0 * in1.x - (((in1.y + l1) + in2.x) + in0.x);
+            lap1.y = 4.0 * in1.y - (((r1 + in1.x) + in2.y) + in0.y);
+            double lapr1 = __shfl_down_sync(0xffffffffu, lap1.x, 1);  // lap(b+1, jr+1)
+            // fluxes of row jr
+            double2 fly;
+            fly.x = limit<LIMITER>(lap1.x - lap0.x, in1.x - in0.x);
+            fly.y = limit<LIMITER>(lap1.y - lap0.y, in1.y - in0.y);
+            double fa = limit<LIMITER>(lap0.y - lap0.x, in0.y - in0.x);  // flx(a, jr)
+            double fb = limit<LIMITER>(lapr0 - lap0.y, r0 - in0.y);      // flx(b, jr)
+            double fl = __shfl_up_sync(0xffffffffu, fb, 1);              // flx(a-1, jr)
+            if (jr >= j0 && jr < jend) {
+                double2 o;
+                o.x = in0.x - co.x * (((fa - fl) + fly.x) - flym1.x);
+                o.y = in0.y - co.y * (((fb - fa) + fly.y) - flym1.y);
+                double *row = pout + (int64_t)jr * out.sj;
+                if (store_y) __stcs(reinterpret_cast<double2 *>(row + col), o);
+                else if (store_x) __stcs(row + col, o.x);
+            }
+            // roll
+            in0 = in1; in1 = in2; lap0 = lap1; flym1 = fly; r0 = r1; lapr0 = lapr1;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// host dispatch
+// ------------------------------------------------------------------------------------------------
+template <bool LIMITER>
+static int launch_hdiff(View3<const double> in, View3<double> out, View3<const double> co,
+                        const int64_t domain[3], int variant, cudaStream_t stream)
+{
+    const int ni = (int)domain[0], nj = (int)domain[1], nk = (int)domain[2];
+    const bool fast_ok = in.si == 1 && out.si == 1 && co.si == 1 && aligned16(in.p) &&
+                         aligned16(out.p) && aligned16(co.p) && (in.sj % 2 == 0) &&
+                         (in.sk % 2 == 0) && (out.sj % 2 == 0) && (out.sk % 2 == 0) &&
+                         (co.sj % 2 == 0) && (co.sk % 2 == 0);
+    if (variant == 0) variant = fast_ok ? 2 : 1;
+    if (variant == 1) {
+        dim3 block(64, 4, 1);
+        dim3 grid((ni + 63) / 64, (nj + 3) / 4, nk);
+        hdiff_point<LIMITER><<<grid, block, 0, stream>>>(in, out, co, ni, nj, nk);
+    } else if (variant == 2 || variant == 3) {
+        if (!fast_ok) {
+            set_error("hdiff variant %d needs unit I stride, 16-byte aligned origins and even J/K strides", variant);
+            return B200_EUNSUP;
+        }
+        const int nwarps = (ni + JM_COLS_PER_WARP - 1) / JM_COLS_PER_WARP;
+        int wpb = nwarps < 8 ? nwarps : 8;
+        if (nwarps > 8) {  // fewest padded warps, prefer wider blocks
+            int best = 1 << 30;
+            for (int w = 8; w >= 4; --w) {
+                int padded = (nwarps + w - 1) / w * w;
+                if (padded < best) { best = padded; wpb = w; }
+            }
+        }
+        static const int env_tj = env_int("B200_HDIFF_TJ", 0);  // tuning hook (read once)
+        const int tj = env_tj > 0 ? env_tj : (nj >= 256 ? 32 : (nj >= 64 ? 16 : 8));
+        dim3 block(32 * wpb, 1, 1);
+        dim3 grid((nwarps + wpb - 1) / wpb, (nj + tj - 1) / tj, nk);
+        if (variant == 2)
+            hdiff_jmarch<LIMITER, 2><<<grid, block, 0, stream>>>(in, out, co, ni, nj, nk, tj);
+        else
+            hdiff_jmarch<LIMITER, 4><<<grid, block, 0, stream>>>(in, out, co, ni, nj, nk, tj);
+    } else {
+        set_error("hdiff: unknown variant %d", variant);
+        return B200_EUNSUP;
+    }
+    B200_CUDA_CHECK(cudaGetLastError());
+    return B200_OK;
+}
+
+}  // namespace b200
+
+extern "C" int b200_hdiff(const b200_field *in_field, const b200_field *out_field,
+                          const b200_field *coeff, const int64_t domain[3], int limiter,
+                          int variant, void *stream)
+{
+    using namespace b200;
+    B200_REQUIRE(domain, "domain is null");
+    B200_REQUIRE(domain[0] >= 0 && domain[1] >= 0 && domain[2] >= 0, "negative domain");
+    B200_REQUIRE(domain[0] < (1 << 30) && domain[1] < (1 << 30) && domain[2] < 65536,
+                 "domain too large");
+    const int h2[3] = {2, 2, 0}, h0[3] = {0, 0, 0};
+    View3<const double> in, co;
+    View3<double> out;
+    int rc;
+    if ((rc = make_view<const double>(in_field, "in_field", B200_FLOAT64, domain, h2, h2, &in))) return rc;
+    if ((rc = make_view<double>(out_field, "out_field", B200_FLOAT64, domain, h0, h0, &out))) return rc;
+    if ((rc = make_view<const double>(coeff, "coeff", B200_FLOAT64, domain, h0, h0, &co))) return rc;
+    if (domain[0] == 0 || domain[1] == 0 || domain[2] == 0) return B200_OK;
+    return limiter ? launch_hdiff<true>(in, out, co, domain, variant, (cudaStream_t)stream)
+                   : launch_hdiff<false>(in, out, co, domain, variant, (cudaStream_t)stream);
+}

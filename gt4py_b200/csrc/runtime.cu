@@ -1,0 +1,193 @@
+// runtime.cu -- device, memory, stream/event and module-launch entry points of the C ABI.
+#include <cstring>
+
+#include "common.cuh"
+
+namespace b200 {
+static thread_local char g_err[1024] = "";
+void set_error(const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+}  // namespace b200
+
+extern "C" {
+
+int b200_abi_version(void) { return B200_ABI_VERSION; }
+const char *b200_last_error(void) { return b200::g_err; }
+
+int b200_device_count(int *count)
+{
+    B200_REQUIRE(count, "count is null");
+    B200_CUDA_CHECK(cudaGetDeviceCount(count));
+    return B200_OK;
+}
+int b200_set_device(int device)
+{
+    B200_CUDA_CHECK(cudaSetDevice(device));
+    return B200_OK;
+}
+int b200_get_device(int *device)
+{
+    B200_CUDA_CHECK(cudaGetDevice(device));
+    return B200_OK;
+}
+int b200_device_sync(void)
+{
+    B200_CUDA_CHECK(cudaDeviceSynchronize());
+    return B200_OK;
+}
+int b200_device_props(int64_t props[8])
+{
+    int dev = 0;
+    B200_CUDA_CHECK(cudaGetDevice(&dev));
+    cudaDeviceProp p;
+    B200_CUDA_CHECK(cudaGetDeviceProperties(&p, dev));
+    props[0] = p.multiProcessorCount;
+    props[1] = (int64_t)p.sharedMemPerBlockOptin;
+    props[2] = p.l2CacheSize;
+    props[3] = p.major;
+    props[4] = p.minor;
+    props[5] = (int64_t)(p.totalGlobalMem >> 20);
+    props[6] = props[7] = 0;
+    return B200_OK;
+}
+
+int b200_malloc(void **dptr, size_t bytes)
+{
+    B200_REQUIRE(dptr, "dptr is null");
+    cudaError_t e = cudaMalloc(dptr, bytes ? bytes : 1);
+    if (e == cudaErrorMemoryAllocation) {
+        b200::set_error("cudaMalloc(%zu bytes): out of device memory", bytes);
+        return B200_ENOMEM;
+    }
+    B200_CUDA_CHECK(e);
+    return B200_OK;
+}
+int b200_free(void *dptr)
+{
+    B200_CUDA_CHECK(cudaFree(dptr));
+    return B200_OK;
+}
+int b200_host_alloc(void **hptr, size_t bytes)
+{
+    B200_REQUIRE(hptr, "hptr is null");
+    B200_CUDA_CHECK(cudaMallocHost(hptr, bytes ? bytes : 1));
+    return B200_OK;
+}
+int b200_host_free(void *hptr)
+{
+    B200_CUDA_CHECK(cudaFreeHost(hptr));
+    return B200_OK;
+}
+static int copy(void *dst, const void *src, size_t bytes, void *stream, cudaMemcpyKind kind)
+{
+    if (bytes == 0) return B200_OK;
+    B200_REQUIRE(dst && src, "memcpy: null pointer");
+    B200_CUDA_CHECK(cudaMemcpyAsync(dst, src, bytes, kind, (cudaStream_t)stream));
+    if (!stream) B200_CUDA_CHECK(cudaStreamSynchronize(0));
+    return B200_OK;
+}
+int b200_memcpy_h2d(void *d, const void *s, size_t n, void *st) { return copy(d, s, n, st, cudaMemcpyHostToDevice); }
+int b200_memcpy_d2h(void *d, const void *s, size_t n, void *st) { return copy(d, s, n, st, cudaMemcpyDeviceToHost); }
+int b200_memcpy_d2d(void *d, const void *s, size_t n, void *st) { return copy(d, s, n, st, cudaMemcpyDeviceToDevice); }
+int b200_memset(void *dst, int value, size_t bytes, void *stream)
+{
+    if (bytes == 0) return B200_OK;
+    B200_CUDA_CHECK(cudaMemsetAsync(dst, value, bytes, (cudaStream_t)stream));
+    return B200_OK;
+}
+
+int b200_stream_create(void **stream)
+{
+    cudaStream_t s;
+    B200_CUDA_CHECK(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+    *stream = s;
+    return B200_OK;
+}
+int b200_stream_destroy(void *stream)
+{
+    B200_CUDA_CHECK(cudaStreamDestroy((cudaStream_t)stream));
+    return B200_OK;
+}
+int b200_stream_sync(void *stream)
+{
+    B200_CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream));
+    return B200_OK;
+}
+int b200_event_create(void **event)
+{
+    cudaEvent_t e;
+    B200_CUDA_CHECK(cudaEventCreate(&e));
+    *event = e;
+    return B200_OK;
+}
+int b200_event_destroy(void *event)
+{
+    B200_CUDA_CHECK(cudaEventDestroy((cudaEvent_t)event));
+    return B200_OK;
+}
+int b200_event_record(void *event, void *stream)
+{
+    B200_CUDA_CHECK(cudaEventRecord((cudaEvent_t)event, (cudaStream_t)stream));
+    return B200_OK;
+}
+int b200_event_sync(void *event)
+{
+    B200_CUDA_CHECK(cudaEventSynchronize((cudaEvent_t)event));
+    return B200_OK;
+}
+int b200_event_elapsed_ms(void *start, void *stop, float *ms)
+{
+    B200_CUDA_CHECK(cudaEventElapsedTime(ms, (cudaEvent_t)start, (cudaEvent_t)stop));
+    return B200_OK;
+}
+int b200_stream_wait_event(void *stream, void *event)
+{
+    B200_CUDA_CHECK(cudaStreamWaitEvent((cudaStream_t)stream, (cudaEvent_t)event, 0));
+    return B200_OK;
+}
+
+// ---- generated-stencil modules: cubin images built by the Python backend with nvcc ----------
+int b200_module_load(const void *image, size_t bytes, void **module)
+{
+    B200_REQUIRE(image && bytes && module, "module_load: bad arguments");
+    cudaLibrary_t lib;
+    B200_CUDA_CHECK(cudaLibraryLoadData(&lib, image, nullptr, nullptr, 0, nullptr, nullptr, 0));
+    *module = lib;
+    return B200_OK;
+}
+int b200_module_unload(void *module)
+{
+    B200_CUDA_CHECK(cudaLibraryUnload((cudaLibrary_t)module));
+    return B200_OK;
+}
+int b200_module_get_kernel(void *module, const char *name, void **kernel)
+{
+    cudaKernel_t k;
+    B200_CUDA_CHECK(cudaLibraryGetKernel(&k, (cudaLibrary_t)module, name));
+    *kernel = k;
+    return B200_OK;
+}
+int b200_kernel_set_smem(void *kernel, int dynamic_smem_bytes)
+{
+    B200_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         dynamic_smem_bytes));
+    return B200_OK;
+}
+int b200_launch(void *kernel, const uint32_t grid[3], const uint32_t block[3],
+                uint32_t dynamic_smem_bytes, void *stream, void **args, int nargs)
+{
+    (void)nargs;
+    B200_REQUIRE(kernel && grid && block, "launch: bad arguments");
+    if (grid[0] == 0 || grid[1] == 0 || grid[2] == 0) return B200_OK;  // empty domain
+    B200_CUDA_CHECK(cudaLaunchKernel(kernel, dim3(grid[0], grid[1], grid[2]),
+                                     dim3(block[0], block[1], block[2]), args, dynamic_smem_bytes,
+                                     (cudaStream_t)stream));
+    return B200_OK;
+}
+
+}  // extern "C"

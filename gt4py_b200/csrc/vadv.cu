@@ -1,0 +1,304 @@
+// vadv.cu -- COSMO vertical advection (tridiagonal set-up + Thomas solve), hand-written for sm_100a.
+//
+// Reference semantics: vertical_advection_dycore, tests/cartesian_tests/integration_tests/
+// multi_feature_tests/stencil_definitions.py:235-313 of the reference (externals BET_M=BET_P=0.5).
+// Operator association follows the definition exactly; compiled with -fmad=false and IEEE division,
+// so results are bit-identical to the reference numpy backend.
+//
+// Kernels
+//   vadv_column<PF> (variant 2): one thread per (i, j) column, warps along the contiguous I axis.
+//       FORWARD sweep keeps u_stage[k-1..k+1] and the wcon pair sums in registers (rolling buffer),
+//       prefetches PF levels ahead, and pushes the Thomas coefficients ccol/dcol of every level
+//       onto a per-thread LIFO in SHARED MEMORY ([level][thread], conflict-free); the BACKWARD sweep
+//       pops them.  ccol/dcol/datacol therefore never touch HBM: DRAM traffic is the 5 input
+//       fields + 1 output (48 B/point) plus the backward re-read of u_pos (normally an L2 hit).
+//   vadv_column_gmem (variant 1): same arithmetic, LIFO in a global scratch buffer; works for any
+//       nk and any strides (safe path, also the "GridTools-style" 80 B/point baseline).
+#include "common.cuh"
+
+namespace b200 {
+
+struct VadvArgs {
+    View3<double> utens_stage;
+    View3<const double> u_stage, wcon, u_pos, utens;
+    double dtr_stage;
+    int ni, nj, nk;
+};
+
+constexpr double BET_M = 0.5, BET_P = 0.5;
+
+// One level's worth of inputs (what a forward step loads).
+struct Lvl {
+    double w0, w1;  // wcon(i, k+1), wcon(i+1, k+1)
+    double us;      // u_stage(k+1)
+    double up, ut, uts;  // u_pos(k), utens(k), utens_stage(k)
+};
+
+struct Ptrs {
+    const double *__restrict__ us, *__restrict__ w0, *__restrict__ w1, *__restrict__ up,
+        *__restrict__ ut;
+    double *__restrict__ uts;
+    int64_t sk_us, sk_w, sk_up, sk_ut, sk_uts;
+};
+
+__device__ __forceinline__ Lvl load_level(const Ptrs &p, int k, int nk)
+{
+    Lvl l;
+    if (k < nk) {
+        l.up = __ldg(p.up + k * p.sk_up);
+        l.ut = __ldcs(p.ut + k * p.sk_ut);
+        l.uts = __ldcs(p.uts + k * p.sk_uts);
+    } else {
+        l.up = l.ut = l.uts = 0.0;
+    }
+    if (k + 1 < nk) {
+        l.w0 = __ldg(p.w0 + (k + 1) * p.sk_w);
+        l.w1 = __ldg(p.w1 + (k + 1) * p.sk_w);
+        l.us = __ldcs(p.us + (k + 1) * p.sk_us);
+    } else {
+        l.w0 = l.w1 = l.us = 0.0;
+    }
+    return l;
+}
+
+// Rolling state carried through the forward sweep.
+struct Fwd {
+    double us_m1, us_0;  // u_stage(k-1), u_stage(k)
+    double wsum;         // wcon(i+1,k) + wcon(i,k)
+    double ccol_m1, dcol_m1;
+};
+
+// Forward step of level k (section chosen by k).  Returns (ccol, dcol) of the level.
+__device__ __forceinline__ void forward_level(const Lvl &l, Fwd &s, double dtr, int k, int nk,
+                                              double &ccol, double &dcol)
+{
+    const double wsum_p1 = l.w1 + l.w0;  // wcon[1,0,1] + wcon[0,0,1]
+    const double us_p1 = l.us;
+    if (k == 0) {  // interval(0, 1)  :248-264
+        double gcv = 0.25 * wsum_p1;
+        double cs = gcv * BET_M;
+        double cc = gcv * BET_P;
+        double bcol = dtr - cc;
+        double correction = -cs * (us_p1 - s.us_0);
+        double dc = ((dtr * l.up + l.ut) + l.uts) + correction;
+        double divided = 1.0 / bcol;
+        ccol = cc * divided;
+        dcol = dc * divided;
+    } else if (k < nk - 1) {  // interval(1, -1)  :266-287
+        double gav = -0.25 * s.wsum;
+        double gcv = 0.25 * wsum_p1;
+        double as_ = gav * BET_M;
+        double cs = gcv * BET_M;
+        double acol = gav * BET_P;
+        double cc = gcv * BET_P;
+        double bcol = (dtr - acol) - cc;
+        double correction = -as_ * (s.us_m1 - s.us_0) - cs * (us_p1 - s.us_0);
+        double dc = ((dtr * l.up + l.ut) + l.uts) + correction;
+        double divided = 1.0 / (bcol - s.ccol_m1 * acol);
+        ccol = cc * divided;
+        dcol = (dc - s.dcol_m1 * acol) * divided;
+    } else {  // interval(-1, None)  :289-303
+        double gav = -0.25 * s.wsum;
+        double as_ = gav * BET_M;
+        double acol = gav * BET_P;
+        double bcol = dtr - acol;
+        double correction = -as_ * (s.us_m1 - s.us_0);
+        double dc = ((dtr * l.up + l.ut) + l.uts) + correction;
+        double divided = 1.0 / (bcol - s.ccol_m1 * acol);
+        ccol = s.ccol_m1;  // ccol is not assigned on the last level (unused by the backward sweep)
+        dcol = (dc - s.dcol_m1 * acol) * divided;
+    }
+    s.us_m1 = s.us_0;
+    s.us_0 = us_p1;
+    s.wsum = wsum_p1;
+    s.ccol_m1 = ccol;
+    s.dcol_m1 = dcol;
+}
+
+__device__ __forceinline__ Ptrs make_ptrs(const VadvArgs &a, int i, int j)
+{
+    Ptrs p;
+    p.us = a.u_stage.p + i * a.u_stage.si + j * a.u_stage.sj;
+    p.w0 = a.wcon.p + i * a.wcon.si + j * a.wcon.sj;
+    p.w1 = p.w0 + a.wcon.si;
+    p.up = a.u_pos.p + i * a.u_pos.si + j * a.u_pos.sj;
+    p.ut = a.utens.p + i * a.utens.si + j * a.utens.sj;
+    p.uts = a.utens_stage.p + i * a.utens_stage.si + j * a.utens_stage.sj;
+    p.sk_us = a.u_stage.sk;
+    p.sk_w = a.wcon.sk;
+    p.sk_up = a.u_pos.sk;
+    p.sk_ut = a.utens.sk;
+    p.sk_uts = a.utens_stage.sk;
+    return p;
+}
+
+// LIFO accessors: STASH(k) -> reference to the (ccol, dcol) slot of level k for this thread.
+template <int PF, typename Stash>
+__device__ __forceinline__ void vadv_sweeps(const VadvArgs &a, const Ptrs &p, Stash stash)
+{
+    const int nk = a.nk;
+    const double dtr = a.dtr_stage;
+    // ---- FORWARD ----
+    Fwd s;
+    s.us_m1 = 0.0;
+    s.us_0 = __ldcs(p.us);
+    s.wsum = 0.0;
+    s.ccol_m1 = s.dcol_m1 = 0.0;
+    Lvl q[PF];
+#pragma unroll
+    for (int u = 0; u < PF; ++u) q[u] = load_level(p, u, nk);
+    for (int kb = 0; kb < nk; kb += PF) {
+#pragma unroll
+        for (int u = 0; u < PF; ++u) {
+            const int k = kb + u;
+            if (k < nk) {
+                Lvl l = q[u];
+                q[u] = load_level(p, k + PF, nk);
+                double cc, dc;
+                forward_level(l, s, dtr, k, nk, cc, dc);
+                stash(k, cc, dc, /*store=*/true);
+            }
+        }
+    }
+    // ---- BACKWARD ----  :305-312
+    double upq[PF];
+#pragma unroll
+    for (int u = 0; u < PF; ++u) upq[u] = (nk - 1 - u >= 0) ? __ldg(p.up + (nk - 1 - u) * p.sk_up) : 0.0;
+    double datacol = 0.0;
+    for (int kb = nk - 1; kb >= 0; kb -= PF) {
+#pragma unroll
+        for (int u = 0; u < PF; ++u) {
+            const int k = kb - u;
+            if (k >= 0) {
+                double up = upq[u];
+                upq[u] = (k - PF >= 0) ? __ldg(p.up + (k - PF) * p.sk_up) : 0.0;
+                double cc, dc;
+                stash(k, cc, dc, /*store=*/false);
+                datacol = (k == nk - 1) ? dc : dc - cc * datacol;
+                __stcs(p.uts + k * p.sk_uts, dtr * (datacol - up));
+            }
+        }
+    }
+}
+
+template <int PF>
+__global__ void __launch_bounds__(160, 1) vadv_column(VadvArgs a, int tpb)
+{
+    extern __shared__ double smem[];  // [nk][2][tpb]
+    const int t = threadIdx.x;
+    const int i = blockIdx.x * 32 + (t & 31);
+    const int j = blockIdx.y * (tpb >> 5) + (t >> 5);
+    if (i >= a.ni || j >= a.nj) return;
+    Ptrs p = make_ptrs(a, i, j);
+    double *base = smem + t;
+    const int lv = 2 * tpb;
+    vadv_sweeps<PF>(a, p, [=](int k, double &cc, double &dc, bool store) {
+        double *slot = base + k * lv;
+        if (store) {
+            slot[0] = cc;
+            slot[tpb] = dc;
+        } else {
+            cc = slot[0];
+            dc = slot[tpb];
+        }
+    });
+}
+
+__global__ void __launch_bounds__(128) vadv_column_gmem(VadvArgs a, double *scratch)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y;
+    if (i >= a.ni || j >= a.nj) return;
+    Ptrs p = make_ptrs(a, i, j);
+    const int64_t cols = (int64_t)a.ni * a.nj;
+    double *base = scratch + (int64_t)j * a.ni + i;
+    vadv_sweeps<2>(a, p, [=](int k, double &cc, double &dc, bool store) {
+        double *slot = base + (int64_t)k * 2 * cols;
+        if (store) {
+            slot[0] = cc;
+            slot[cols] = dc;
+        } else {
+            cc = slot[0];
+            dc = slot[cols];
+        }
+    });
+}
+
+// scratch for the global-memory variant, grown on demand (per process; guarded by the caller's
+// stream ordering: launches on different streams that need scratch are not supported concurrently)
+static double *g_scratch = nullptr;
+static size_t g_scratch_bytes = 0;
+
+}  // namespace b200
+
+extern "C" int b200_vadv(const b200_field *utens_stage, const b200_field *u_stage,
+                         const b200_field *wcon, const b200_field *u_pos, const b200_field *utens,
+                         double dtr_stage, const int64_t domain[3], int variant, void *stream_)
+{
+    using namespace b200;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    B200_REQUIRE(domain, "domain is null");
+    B200_REQUIRE(domain[0] >= 0 && domain[1] >= 0 && domain[2] >= 0, "negative domain");
+    B200_REQUIRE(domain[0] < (1 << 30) && domain[1] < (1 << 30), "domain too large");
+    if (domain[0] == 0 || domain[1] == 0 || domain[2] == 0) return B200_OK;
+    B200_REQUIRE(domain[2] >= 3, "vadv needs at least 3 vertical levels (got %lld)",
+                 (long long)domain[2]);
+    const int h0[3] = {0, 0, 0}, hw[3] = {1, 0, 0};
+    VadvArgs a;
+    int rc;
+    if ((rc = make_view<double>(utens_stage, "utens_stage", B200_FLOAT64, domain, h0, h0, &a.utens_stage))) return rc;
+    if ((rc = make_view<const double>(u_stage, "u_stage", B200_FLOAT64, domain, h0, h0, &a.u_stage))) return rc;
+    if ((rc = make_view<const double>(wcon, "wcon", B200_FLOAT64, domain, h0, hw, &a.wcon))) return rc;
+    if ((rc = make_view<const double>(u_pos, "u_pos", B200_FLOAT64, domain, h0, h0, &a.u_pos))) return rc;
+    if ((rc = make_view<const double>(utens, "utens", B200_FLOAT64, domain, h0, h0, &a.utens))) return rc;
+    a.dtr_stage = dtr_stage;
+    a.ni = (int)domain[0];
+    a.nj = (int)domain[1];
+    a.nk = (int)domain[2];
+
+    static int max_smem = -1;
+    if (max_smem < 0) {
+        int dev = 0;
+        B200_CUDA_CHECK(cudaGetDevice(&dev));
+        B200_CUDA_CHECK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+    }
+    // threads per block for the smem-LIFO kernel: as many warps as the LIFO allows, at most 5
+    int warps = (int)(max_smem / ((size_t)a.nk * 16 * 32));
+    if (warps > 5) warps = 5;
+    if (variant == 0) variant = warps >= 1 ? 2 : 1;
+
+    if (variant == 2 || variant == 3) {
+        if (warps < 1) {
+            set_error("vadv variant %d: nk=%d does not fit the shared-memory LIFO", variant, a.nk);
+            return B200_EUNSUP;
+        }
+        static const int env_w = env_int("B200_VADV_WARPS", 0);
+        if (env_w > 0 && env_w < warps) warps = env_w;
+        const int tpb = warps * 32;
+        const size_t smem = (size_t)a.nk * 16 * tpb;
+        dim3 grid((a.ni + 31) / 32, (a.nj + warps - 1) / warps, 1);
+        if (variant == 2) {
+            B200_CUDA_CHECK(cudaFuncSetAttribute(vadv_column<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            vadv_column<4><<<grid, tpb, smem, stream>>>(a, tpb);
+        } else {
+            B200_CUDA_CHECK(cudaFuncSetAttribute(vadv_column<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            vadv_column<8><<<grid, tpb, smem, stream>>>(a, tpb);
+        }
+    } else if (variant == 1) {
+        size_t need = (size_t)a.ni * a.nj * a.nk * 16;
+        if (need > g_scratch_bytes) {
+            if (g_scratch) B200_CUDA_CHECK(cudaFree(g_scratch));
+            g_scratch = nullptr;
+            g_scratch_bytes = 0;
+            B200_CUDA_CHECK(cudaMalloc(&g_scratch, need));
+            g_scratch_bytes = need;
+        }
+        dim3 grid((a.ni + 127) / 128, a.nj, 1);
+        vadv_column_gmem<<<grid, 128, 0, stream>>>(a, g_scratch);
+    } else {
+        set_error("vadv: unknown variant %d", variant);
+        return B200_EUNSUP;
+    }
+    B200_CUDA_CHECK(cudaGetLastError());
+    return B200_OK;
+}

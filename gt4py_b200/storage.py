@@ -1,0 +1,372 @@
+"""Device storage for the b200 backend: the cupy-free counterpart of ``gt4py.storage``.
+
+Mirrors /root/reference/src/gt4py/storage/cartesian/interface.py:40-327 (``empty / zeros / ones /
+full / from_array`` with ``backend=, aligned_index=, dimensions=``) and the padded / aligned
+allocation algorithm of /root/reference/src/gt4py/storage/allocators.py:189-275:
+
+* the layout is I-contiguous -- ``layout_map (2, 1, 0)`` like ``gt:gpu``
+  (storage/cartesian/layout_registry.py:105-113), data dimensions outermost;
+* only the contiguous dimension is padded, to a multiple of ``ALIGNMENT`` elements;
+* the allocation start is shifted so that ``aligned_index`` (the origin of the compute domain)
+  falls on an ``ALIGNMENT * itemsize`` byte boundary.
+
+sm_100a defaults: ``ALIGNMENT = 16`` elements, i.e. one 128-byte L2 line for float64, which makes
+every I-row of the compute domain start on a line boundary and keeps the 128-bit vector loads of
+the kernels aligned.
+
+Arrays are ``DeviceArray`` objects: a thin owner of ``cudaMalloc`` memory exposing
+``__cuda_array_interface__`` (v3), so they interoperate with cupy / torch / numba without any of
+them being imported here.
+"""
+from __future__ import annotations
+
+import math
+import numbers
+from ctypes import byref, c_void_p
+from typing import Optional, Sequence, Tuple
+
+import numpy as np
+
+from . import _lib
+
+ALIGNMENT = 16  # elements
+BASE_LAYOUT = (2, 1, 0)
+BACKEND_NAME = "b200"
+
+
+# ---- layout helpers (layout.py:28-57 semantics) ---------------------------------------------------
+def layout_map(dimensions: Sequence[str]) -> Tuple[int, ...]:
+    mask = [d in dimensions for d in "IJK"]
+    ranks = [bl for m, bl in zip(mask, BASE_LAYOUT) if m]
+    ndata = len(dimensions) - sum(mask)
+    ranks = [ndata + r for r in ranks] + list(range(ndata))
+    res = [0] * len(ranks)
+    for i, idx in enumerate(np.argsort(ranks)):
+        res[idx] = i
+    return tuple(res)
+
+
+def is_optimal_layout(array, dimensions: Sequence[str]) -> bool:
+    """True when the strides of `array` are ordered like ``layout_map(dimensions)`` (layout.py:60-80)."""
+    lm = layout_map(tuple(dimensions))
+    strides = _strides_of(array)
+    if len(strides) != len(lm):
+        return False
+    order = sorted(range(len(lm)), key=lambda d: lm[d])  # slowest ... fastest
+    prev = None
+    for d in order:
+        if prev is not None and strides[d] > prev:
+            return False
+        prev = strides[d]
+    return True
+
+
+def _strides_of(array):
+    if isinstance(array, DeviceArray):
+        return array.strides
+    cai = getattr(array, "__cuda_array_interface__", None) or getattr(array, "__array_interface__", None)
+    if cai is not None:
+        st = cai.get("strides")
+        if st is None:
+            shape, item = cai["shape"], np.dtype(cai["typestr"]).itemsize
+            st, acc = [0] * len(shape), item
+            for d in range(len(shape) - 1, -1, -1):
+                st[d] = acc
+                acc *= shape[d]
+        return tuple(st)
+    return tuple(array.strides)
+
+
+def normalize_storage_spec(aligned_index, shape, dtype, dimensions):
+    """utils.py:86-164 of the reference storage package."""
+    if shape is None or isinstance(shape, (str, bytes)) or not all(
+            isinstance(s, numbers.Integral) for s in shape):
+        raise TypeError("shape must be an iterable of ints.")
+    shape = tuple(int(s) for s in shape)
+    if dimensions is None:
+        dimensions = list("IJK"[: len(shape)]) if len(shape) <= 3 else list("IJK") + [
+            str(d) for d in range(len(shape) - 3)]
+    dimensions = tuple(getattr(d, "__gt_axis_name__", d) for d in dimensions)
+    if not all(isinstance(d, str) and (d.isdigit() or d in "IJK") for d in dimensions):
+        raise ValueError(f"Invalid dimensions definition: '{dimensions}'")
+    if len(shape) != len(dimensions):
+        raise ValueError(f"Dimensions ({dimensions}) and shape ({shape}) have non-matching sizes.")
+    if any(s <= 0 for s in shape):
+        raise ValueError(f"shape ({shape}) contains non-positive value.")
+    if aligned_index is None:
+        aligned_index = (0,) * len(shape)
+    if isinstance(aligned_index, (str, bytes)) or not all(
+            isinstance(i, numbers.Integral) for i in aligned_index):
+        raise TypeError("aligned_index must be an iterable of ints.")
+    aligned_index = tuple(int(i) for i in aligned_index)
+    if len(aligned_index) != len(shape):
+        raise ValueError(f"Shape ({shape}) and aligned_index ({aligned_index}) have non-matching sizes.")
+    if any(i < 0 for i in aligned_index):
+        raise ValueError(f"aligned_index ({aligned_index}) contains negative value.")
+    dtype = np.dtype(dtype)
+    if dtype.shape:
+        sub_dtype, sub_shape = dtype.subdtype
+        aligned_index = (*aligned_index, *((0,) * dtype.ndim))
+        shape = (*shape, *sub_shape)
+        dimensions = (*dimensions, *(str(d) for d in range(dtype.ndim)))
+        dtype = sub_dtype
+    return aligned_index, shape, dtype, dimensions
+
+
+class _Buffer:
+    """Owner of one cudaMalloc allocation."""
+
+    def __init__(self, nbytes: int):
+        p = c_void_p()
+        _lib.check(_lib.lib().b200_malloc(byref(p), nbytes))
+        self.ptr = p.value
+        self.nbytes = nbytes
+
+    def __del__(self):
+        try:
+            if self.ptr:
+                _lib.lib().b200_free(c_void_p(self.ptr))
+                self.ptr = None
+        except Exception:
+            pass
+
+
+class DeviceArray:
+    """N-d strided view of device memory (no arithmetic: data lives on the GPU for the kernels).
+
+    Exposes ``__cuda_array_interface__`` v3, ``shape / strides (bytes) / dtype / ndim``, basic
+    slicing (views), ``asnumpy()``, ``set()`` and ``fill()``.
+    """
+
+    __slots__ = ("_buf", "ptr", "shape", "strides", "dtype", "__gt_dims__", "__gt_origin__", "__weakref__")
+
+    def __init__(self, buf, ptr, shape, strides, dtype, dims=None, origin=None):
+        self._buf = buf
+        self.ptr = int(ptr)
+        self.shape = tuple(int(s) for s in shape)
+        self.strides = tuple(int(s) for s in strides)
+        self.dtype = np.dtype(dtype)
+        self.__gt_dims__ = dims
+        self.__gt_origin__ = origin
+
+    # -- protocol ---------------------------------------------------------------------------
+    @property
+    def __cuda_array_interface__(self):
+        return {
+            "shape": self.shape,
+            "typestr": self.dtype.str,
+            "data": (self.ptr, False),
+            "version": 3,
+            "strides": self.strides,
+            "descr": [("", self.dtype.str)],
+            "stream": None,
+        }
+
+    @property
+    def ndim(self):
+        return len(self.shape)
+
+    @property
+    def size(self):
+        return int(np.prod(self.shape, dtype=np.int64)) if self.shape else 1
+
+    @property
+    def itemsize(self):
+        return self.dtype.itemsize
+
+    @property
+    def nbytes(self):
+        return self.size * self.itemsize
+
+    @property
+    def device(self):
+        return "gpu"
+
+    def __len__(self):
+        return self.shape[0]
+
+    def __repr__(self):
+        return f"DeviceArray(shape={self.shape}, dtype={self.dtype}, strides={self.strides}, ptr=0x{self.ptr:x})"
+
+    # -- byte extent of the view ---------------------------------------------------------------
+    def _extent(self):
+        """(lowest byte offset, one-past-highest byte offset) relative to self.ptr."""
+        lo = hi = 0
+        if self.size == 0:
+            return 0, 0
+        for n, s in zip(self.shape, self.strides):
+            if s >= 0:
+                hi += (n - 1) * s
+            else:
+                lo += (n - 1) * s
+        return lo, hi + self.itemsize
+
+    # -- host transfer ---------------------------------------------------------------------------
+    def asnumpy(self, stream=None) -> np.ndarray:
+        """Copy to host; the result has the same shape and stride ORDER (a strided view of a copy of
+        the byte extent)."""
+        lo, hi = self._extent()
+        raw = np.empty(hi - lo, dtype=np.uint8)
+        if hi > lo:
+            _lib.check(_lib.lib().b200_memcpy_d2h(raw.ctypes.data, c_void_p(self.ptr + lo), hi - lo,
+                                                  _lib.stream_handle(stream)))
+            if stream is not None:
+                _lib.check(_lib.lib().b200_stream_sync(_lib.stream_handle(stream)))
+        base = raw[-lo:] if lo else raw
+        return np.ndarray(self.shape, dtype=self.dtype, buffer=base.data if self.size else None,
+                          strides=self.strides) if self.size else np.empty(self.shape, self.dtype)
+
+    def __array__(self, dtype=None, copy=None):
+        a = self.asnumpy()
+        return a.astype(dtype) if dtype is not None else a
+
+    def set(self, data, stream=None):
+        """Copy host `data` (broadcastable to self.shape) into the view."""
+        lo, hi = self._extent()
+        if hi <= lo:
+            return self
+        dense = self._is_dense()
+        raw = np.empty(hi - lo, dtype=np.uint8)
+        if not dense:  # keep the bytes in the gaps (padding / other views)
+            _lib.check(_lib.lib().b200_memcpy_d2h(raw.ctypes.data, c_void_p(self.ptr + lo), hi - lo, None))
+        view = np.ndarray(self.shape, dtype=self.dtype, buffer=(raw[-lo:] if lo else raw).data,
+                          strides=self.strides)
+        view[...] = data
+        _lib.check(_lib.lib().b200_memcpy_h2d(c_void_p(self.ptr + lo), raw.ctypes.data, hi - lo,
+                                              _lib.stream_handle(stream)))
+        if stream is not None:  # `raw` is pageable and dies with this frame
+            _lib.check(_lib.lib().b200_stream_sync(_lib.stream_handle(stream)))
+        return self
+
+    def _is_dense(self):
+        lo, hi = self._extent()
+        return lo == 0 and hi == self.nbytes
+
+    def fill(self, value):
+        if self._is_dense() and (value == 0 or self.dtype.itemsize == 1):
+            byte = int(np.array(value, dtype=self.dtype).view(np.uint8)[0]) if value != 0 else 0
+            _lib.check(_lib.lib().b200_memset(c_void_p(self.ptr), byte, self.nbytes, None))
+            return self
+        return self.set(np.asarray(value, dtype=self.dtype))
+
+    def copy(self) -> "DeviceArray":
+        """Device-to-device copy of the whole byte extent (same strides)."""
+        lo, hi = self._extent()
+        buf = _Buffer(max(hi - lo, 1))
+        if hi > lo:
+            _lib.check(_lib.lib().b200_memcpy_d2d(c_void_p(buf.ptr), c_void_p(self.ptr + lo), hi - lo, None))
+        return DeviceArray(buf, buf.ptr - lo, self.shape, self.strides, self.dtype,
+                           self.__gt_dims__, self.__gt_origin__)
+
+    # -- views -----------------------------------------------------------------------------------
+    def __getitem__(self, key):
+        if not isinstance(key, tuple):
+            key = (key,)
+        if any(k is Ellipsis for k in key):
+            idx = key.index(Ellipsis)
+            fill = self.ndim - (len(key) - 1)
+            key = key[:idx] + (slice(None),) * fill + key[idx + 1:]
+        key = key + (slice(None),) * (self.ndim - len(key))
+        if len(key) != self.ndim:
+            raise IndexError("too many indices for DeviceArray")
+        ptr, shape, strides = self.ptr, [], []
+        for k, n, s in zip(key, self.shape, self.strides):
+            if isinstance(k, numbers.Integral):
+                k = int(k)
+                if k < 0:
+                    k += n
+                if not 0 <= k < n:
+                    raise IndexError("index out of range")
+                ptr += k * s
+            elif isinstance(k, slice):
+                start, stop, step = k.indices(n)
+                ptr += start * s
+                shape.append(len(range(start, stop, step)))
+                strides.append(s * step)
+            else:
+                raise TypeError("DeviceArray supports only int / slice / Ellipsis indexing")
+        return DeviceArray(self._buf, ptr, shape, strides, self.dtype)
+
+    def __setitem__(self, key, value):
+        self[key].set(value.asnumpy() if isinstance(value, DeviceArray) else value)
+
+    def transpose(self, *axes):
+        if len(axes) == 1 and not isinstance(axes[0], numbers.Integral):
+            axes = tuple(axes[0])
+        if not axes:
+            axes = tuple(reversed(range(self.ndim)))
+        return DeviceArray(self._buf, self.ptr, [self.shape[a] for a in axes],
+                           [self.strides[a] for a in axes], self.dtype)
+
+
+# ---- public interface (interface.py:40-327) ------------------------------------------------------
+def _check_backend(backend):
+    if backend != BACKEND_NAME:
+        raise RuntimeError(f"Storage preset '{backend}' is not registered in gt4py_b200.storage "
+                           f"(only '{BACKEND_NAME}').")
+
+
+def empty(shape, dtype=np.float64, *, backend: str = BACKEND_NAME,
+          aligned_index: Optional[Sequence[int]] = None,
+          dimensions: Optional[Sequence[str]] = None) -> DeviceArray:
+    _check_backend(backend)
+    aligned_index, shape, dtype, dimensions = normalize_storage_spec(aligned_index, shape, dtype, dimensions)
+    lm = layout_map(dimensions)
+    item = dtype.itemsize
+    ndim = len(shape)
+    byte_alignment = ALIGNMENT * item
+    dims_layout = [lm.index(i) for i in range(ndim)]  # slowest ... fastest dimension
+    padded = list(shape)
+    if ndim:
+        c = dims_layout[-1]
+        padded[c] = math.ceil(shape[c] / ALIGNMENT) * ALIGNMENT
+    total = item * int(np.prod(padded, dtype=np.int64)) + (byte_alignment - 1)
+    strides = [item] * ndim
+    acc = item
+    for d in range(ndim - 2, -1, -1):
+        acc = strides[dims_layout[d]] = acc * padded[dims_layout[d + 1]]
+    buf = _Buffer(total)
+    if ndim:
+        c = dims_layout[-1]
+        aligned_off = (ALIGNMENT * math.ceil(aligned_index[c] / ALIGNMENT) - aligned_index[c]) * item
+    else:
+        aligned_off = 0
+    mismatch = (byte_alignment - buf.ptr % byte_alignment) % byte_alignment
+    byte_offset = (aligned_off + mismatch) % byte_alignment
+    return DeviceArray(buf, buf.ptr + byte_offset, shape, strides, dtype)
+
+
+def zeros(shape, dtype=np.float64, *, backend: str = BACKEND_NAME, aligned_index=None, dimensions=None):
+    arr = empty(shape, dtype, backend=backend, aligned_index=aligned_index, dimensions=dimensions)
+    _lib.check(_lib.lib().b200_memset(c_void_p(arr._buf.ptr), 0, arr._buf.nbytes, None))
+    return arr
+
+
+def full(shape, fill_value, dtype=np.float64, *, backend: str = BACKEND_NAME, aligned_index=None, dimensions=None):
+    arr = zeros(shape, dtype, backend=backend, aligned_index=aligned_index, dimensions=dimensions)
+    arr.set(np.asarray(fill_value, dtype=arr.dtype))
+    return arr
+
+
+def ones(shape, dtype=np.float64, *, backend: str = BACKEND_NAME, aligned_index=None, dimensions=None):
+    return full(shape, 1, dtype, backend=backend, aligned_index=aligned_index, dimensions=dimensions)
+
+
+def from_array(data, dtype=None, *, backend: str = BACKEND_NAME, aligned_index=None, dimensions=None):
+    host = data.asnumpy() if isinstance(data, DeviceArray) else np.asarray(data)
+    if dtype is None:
+        dtype = host.dtype
+    dtype = np.dtype(dtype)
+    shape = host.shape
+    if dtype.shape:
+        if shape[-dtype.ndim:] != dtype.shape:
+            raise ValueError(f"Incompatible data shape {shape} with dtype of shape {dtype.shape}.")
+        shape = shape[: -dtype.ndim]
+    arr = zeros(shape, dtype, backend=backend, aligned_index=aligned_index, dimensions=dimensions)
+    arr.set(host)
+    return arr
+
+
+def asnumpy(array) -> np.ndarray:
+    """Host copy of a DeviceArray (or pass-through of a host array)."""
+    return array.asnumpy() if isinstance(array, DeviceArray) else np.asarray(array)

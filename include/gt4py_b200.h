@@ -1,0 +1,141 @@
+/*
+ * gt4py_b200.h -- C ABI of libgt4py_b200.so, the B200 (sm_100a) execution library behind the
+ * "b200" backend of gt4py.cartesian.
+ *
+ * This is the drop-in boundary.  It replaces what the reference reaches through pybind11 in its
+ * generated extension modules:
+ *   - run_computation(domain, field, origin, ..., exec_info)
+ *       /root/reference/src/gt4py/cartesian/backend/gtc_common.py:79-101 (C++ side) and :157-163
+ *       (Python call site)  ->  b200_launch() for generated stencils, and the named entry points
+ *       b200_hdiff / b200_vadv / b200_tridiag for the library's hand-written hot stencils;
+ *   - gt::as_cuda_sid(buffer) + shift_sid_origin(origin)
+ *       gtc_common.py:30-62                       ->  b200_field (raw pointer + element strides +
+ *                                                     origin, read from __cuda_array_interface__);
+ *   - cupy.cuda.Device(0).synchronize()  gtc_common.py:288-296  ->  b200_device_sync / sync flag;
+ *   - cupy device allocation used by gt4py.storage
+ *       /root/reference/src/gt4py/storage/cartesian/utils.py:258-276 -> b200_malloc / b200_free /
+ *                                                     b200_memcpy_*.
+ *
+ * Conventions: plain C types only; every function returns 0 on success or a negative B200_E* code,
+ * with a human-readable message available from b200_last_error() (thread-local).  No function
+ * falls back to a CPU implementation: without a CUDA device compute calls fail with
+ * B200_ECUDA.
+ */
+#ifndef GT4PY_B200_H
+#define GT4PY_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_ABI_VERSION 1
+
+#if defined(__GNUC__)
+#define B200_API __attribute__((visibility("default")))
+#else
+#define B200_API
+#endif
+
+/* error codes */
+#define B200_OK 0
+#define B200_EINVAL -1   /* bad argument (shape, stride, dtype, null pointer)           */
+#define B200_ECUDA -2    /* CUDA runtime error (message holds cudaGetErrorString)       */
+#define B200_EUNSUP -3   /* valid request the library has no kernel for                 */
+#define B200_ENOMEM -4
+
+/* dtype codes (match gt4py.cartesian.gtc.common.DataType ordering, common.py:105-127) */
+#define B200_BOOL 1
+#define B200_INT8 2
+#define B200_INT16 3
+#define B200_INT32 4
+#define B200_INT64 5
+#define B200_FLOAT32 6
+#define B200_FLOAT64 7
+
+#define B200_MAX_DIMS 5
+
+/* One field argument: what as_cuda_sid + shift_sid_origin carry in the reference.
+ * `ptr` is the address of element (0,0,0,...) of the array (NOT origin-shifted); `stride` is in
+ * ELEMENTS per axis, axes ordered I, J, K, data dims; `origin` is the index of the first compute
+ * point; `shape` is the array extent (used for bounds validation only). */
+typedef struct b200_field {
+    void *ptr;
+    int64_t stride[B200_MAX_DIMS];
+    int64_t shape[B200_MAX_DIMS];
+    int32_t origin[B200_MAX_DIMS];
+    int32_t ndim;
+    int32_t dtype;
+} b200_field;
+
+/* ---- library / device ------------------------------------------------------------------- */
+B200_API int b200_abi_version(void);
+B200_API const char *b200_last_error(void);
+B200_API int b200_device_count(int *count);
+B200_API int b200_set_device(int device);
+B200_API int b200_get_device(int *device);
+B200_API int b200_device_sync(void);
+/* props[0]=SM count, [1]=max smem/block optin, [2]=L2 bytes, [3]=cc major, [4]=cc minor,
+ * [5]=total global mem (MiB) */
+B200_API int b200_device_props(int64_t props[8]);
+
+/* ---- memory (device allocations are 256 B aligned by cudaMalloc) ---------------------------- */
+B200_API int b200_malloc(void **dptr, size_t bytes);
+B200_API int b200_free(void *dptr);
+B200_API int b200_host_alloc(void **hptr, size_t bytes); /* pinned */
+B200_API int b200_host_free(void *hptr);
+B200_API int b200_memcpy_h2d(void *dst, const void *src, size_t bytes, void *stream);
+B200_API int b200_memcpy_d2h(void *dst, const void *src, size_t bytes, void *stream);
+B200_API int b200_memcpy_d2d(void *dst, const void *src, size_t bytes, void *stream);
+B200_API int b200_memset(void *dst, int value, size_t bytes, void *stream);
+
+/* ---- streams / events ------------------------------------------------------------------- */
+B200_API int b200_stream_create(void **stream);
+B200_API int b200_stream_destroy(void *stream);
+B200_API int b200_stream_sync(void *stream);
+B200_API int b200_event_create(void **event);
+B200_API int b200_event_destroy(void *event);
+B200_API int b200_event_record(void *event, void *stream);
+B200_API int b200_event_sync(void *event);
+B200_API int b200_event_elapsed_ms(void *start, void *stop, float *ms);
+B200_API int b200_stream_wait_event(void *stream, void *event);
+
+/* ---- hand-written hot stencils ------------------------------------------------------------ */
+/* variant: 0 = auto (fastest kernel whose layout preconditions hold), 1 = generic point kernel
+ * (any strides), >= 2 = a specific tuned kernel (B200_EUNSUP if its preconditions fail).      */
+
+/* horizontal_diffusion(in_field, out_field, coeff): reference definition
+ * tests/cartesian_tests/integration_tests/multi_feature_tests/stencil_definitions.py:316-328.
+ * `limiter` = 1 for that stencil, 0 for simple_horizontal_diffusion (:206-216).
+ * in_field needs a halo of 2 in I and J around `domain`. float64. */
+B200_API int b200_hdiff(const b200_field *in_field, const b200_field *out_field, const b200_field *coeff,
+               const int64_t domain[3], int limiter, int variant, void *stream);
+
+/* vertical_advection_dycore(utens_stage, u_stage, wcon, u_pos, utens, dtr_stage) with externals
+ * BET_M = BET_P = 0.5: stencil_definitions.py:235-313.  wcon is read at i+1.  domain[2] >= 3. */
+B200_API int b200_vadv(const b200_field *utens_stage, const b200_field *u_stage, const b200_field *wcon,
+              const b200_field *u_pos, const b200_field *utens, double dtr_stage,
+              const int64_t domain[3], int variant, void *stream);
+
+/* tridiagonal_solver(inf, diag, sup, rhs, out): stencil_definitions.py:219-232 (sup, rhs updated
+ * in place). */
+B200_API int b200_tridiag(const b200_field *inf, const b200_field *diag, const b200_field *sup,
+                 const b200_field *rhs, const b200_field *out, const int64_t domain[3],
+                 int variant, void *stream);
+
+/* ---- generated stencils (OIR -> CUDA C -> cubin, built by the Python backend) --------------- */
+/* Load a cubin/PTX image, look kernels up by name, launch with a packed argument block.        */
+B200_API int b200_module_load(const void *image, size_t bytes, void **module);
+B200_API int b200_module_unload(void *module);
+B200_API int b200_module_get_kernel(void *module, const char *name, void **kernel);
+B200_API int b200_kernel_set_smem(void *kernel, int dynamic_smem_bytes);
+/* args: array of nargs pointers to the argument values (cudaLaunchKernel convention). */
+B200_API int b200_launch(void *kernel, const uint32_t grid[3], const uint32_t block[3],
+                uint32_t dynamic_smem_bytes, void *stream, void **args, int nargs);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GT4PY_B200_H */

@@ -1,0 +1,166 @@
+"""GPU parity (-m gpu): the CUDA path, called through the C ABI via the stencil objects, against
+ (a) the golden fixtures produced by the reference numpy backend (tests/golden), and
+ (b) the pinned CPU oracle on seeded inputs, incl. ragged sizes and the BASELINE config sizes.
+
+Bar: BIT-EXACT for float64 (stricter than north_star's 1e-12 relative): the kernels keep the
+reference's operator association and are built with -fmad=false.
+"""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+import gt4py_b200 as gb
+from gt4py_b200 import stencils, storage
+from oracle import cpu as oracle
+from oracle import inputs as gen
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def _cases(prefix):
+    return sorted(glob.glob(os.path.join(GOLDEN, prefix + "_[0-9]*.npz")))
+
+
+def _dev(a, origin):
+    return storage.from_array(a, backend="b200", aligned_index=origin)
+
+
+def run_hdiff(f, domain, variant, limiter=True):
+    d = {k: _dev(v, (2, 2, 0)) for k, v in f.items()}
+    if limiter:
+        st = stencils.HorizontalDiffusion.with_variant(variant)
+        st(d["in_field"], d["out_field"], d["coeff"], origin=(2, 2, 0), domain=domain)
+    else:
+        st = stencils.SimpleHorizontalDiffusion.with_variant(variant)
+        st(d["in_field"], d["coeff"], d["out_field"], origin=(2, 2, 0), domain=domain)
+    return d["out_field"].asnumpy()
+
+
+def run_vadv(f, domain, variant):
+    d = {k: _dev(v, (0, 0, 0)) for k, v in f.items() if k != "dtr_stage"}
+    st = stencils.VerticalAdvectionDycore.with_variant(variant)
+    st(d["utens_stage"], d["u_stage"], d["wcon"], d["u_pos"], d["utens"],
+       dtr_stage=f["dtr_stage"], origin=(0, 0, 0), domain=domain)
+    return d["utens_stage"].asnumpy()
+
+
+@pytest.mark.parametrize("variant", [1, 2, 3])
+@pytest.mark.parametrize("path", _cases("hdiff"), ids=os.path.basename)
+def test_hdiff_golden(path, variant):
+    g = np.load(path)
+    dom = tuple(int(x) for x in g["shape"])
+    out = run_hdiff(gen.hdiff_inputs(*dom, seed=int(g["seed"])), dom, variant)
+    assert np.array_equal(out, g["out_field"])  # halo of out_field must stay untouched (zeros)
+
+
+@pytest.mark.parametrize("variant", [1, 2])
+@pytest.mark.parametrize("path", _cases("simple_hdiff"), ids=os.path.basename)
+def test_simple_hdiff_golden(path, variant):
+    g = np.load(path)
+    dom = tuple(int(x) for x in g["shape"])
+    out = run_hdiff(gen.hdiff_inputs(*dom, seed=int(g["seed"])), dom, variant, limiter=False)
+    assert np.array_equal(out, g["out_field"])
+
+
+@pytest.mark.parametrize("variant", [1, 2, 3])
+@pytest.mark.parametrize("path", _cases("vadv"), ids=os.path.basename)
+def test_vadv_golden(path, variant):
+    g = np.load(path)
+    dom = tuple(int(x) for x in g["shape"])
+    out = run_vadv(gen.vadv_inputs(*dom, seed=int(g["seed"])), dom, variant)
+    assert np.array_equal(out, g["utens_stage"])
+
+
+@pytest.mark.parametrize("path", _cases("tridiag"), ids=os.path.basename)
+def test_tridiag_golden(path):
+    g = np.load(path)
+    dom = tuple(int(x) for x in g["shape"])
+    f = gen.tridiag_inputs(*dom, seed=int(g["seed"]))
+    d = {k: _dev(v, (0, 0, 0)) for k, v in f.items()}
+    stencils.tridiagonal_solver(d["inf"], d["diag"], d["sup"], d["rhs"], d["out"], domain=dom)
+    for name in ("sup", "rhs", "out"):
+        assert np.array_equal(d[name].asnumpy(), g[name]), name
+
+
+@pytest.mark.parametrize("variant", [0, 1, 2, 3])
+@pytest.mark.parametrize("dom", [(128, 128, 80), (61, 59, 5), (60, 8, 1), (121, 33, 2), (2, 2, 2),
+                                 (300, 7, 3)])
+def test_hdiff_vs_oracle(dom, variant):
+    f = gen.hdiff_inputs(*dom, seed=123)
+    ref = oracle.hdiff(f["in_field"], f["out_field"].copy(), f["coeff"], domain=dom)
+    out = run_hdiff(f, dom, variant)
+    assert np.array_equal(out, ref)
+
+
+@pytest.mark.parametrize("variant", [0, 1, 2, 3])
+@pytest.mark.parametrize("dom", [(256, 256, 80), (33, 5, 3), (31, 7, 80), (64, 3, 17), (1, 1, 4),
+                                 (100, 6, 137)])
+def test_vadv_vs_oracle(dom, variant):
+    f = gen.vadv_inputs(*dom, seed=99)
+    ref = oracle.vadv(f["utens_stage"].copy(), f["u_stage"], f["wcon"], f["u_pos"], f["utens"],
+                      dtr_stage=f["dtr_stage"], domain=dom)
+    out = run_vadv(f, dom, variant)
+    assert np.array_equal(out, ref)
+
+
+def test_hdiff_subdomain_and_offset_origin():
+    """origin/domain select a sub-box: points outside it must be untouched."""
+    f = gen.hdiff_inputs(40, 30, 4, seed=5)
+    f["out_field"][...] = -7.0
+    origin, dom = (5, 4, 1), (17, 11, 2)
+    d = {k: _dev(v, origin) for k, v in f.items()}
+    stencils.horizontal_diffusion(d["in_field"], d["out_field"], d["coeff"], origin=origin, domain=dom)
+    ref = f["out_field"].copy()
+    oracle.hdiff(f["in_field"], ref, f["coeff"], origin=origin, domain=dom)
+    assert np.array_equal(d["out_field"].asnumpy(), ref)
+
+
+def test_hdiff_non_optimal_layout_uses_generic_kernel():
+    """C-ordered (K-contiguous) device arrays: layout warning, same result."""
+    f = gen.hdiff_inputs(20, 18, 6, seed=8)
+    dom = (20, 18, 6)
+    ref = oracle.hdiff(f["in_field"], f["out_field"].copy(), f["coeff"], domain=dom)
+    d = {}
+    for k, v in f.items():
+        base = storage.from_array(np.ascontiguousarray(v.transpose(2, 1, 0)), backend="b200")
+        d[k] = base.transpose(2, 1, 0)  # logical (I, J, K), strides K-fastest
+    with pytest.warns(UserWarning, match="layout of the field"):
+        stencils.horizontal_diffusion(d["in_field"], d["out_field"], d["coeff"],
+                                      origin=(2, 2, 0), domain=dom)
+    assert np.array_equal(d["out_field"].asnumpy(), ref)
+
+
+def test_full_size_properties_hdiff():
+    """BASELINE config 3 size (1024x1024x80): size-independent properties instead of a full oracle run.
+    (1) constant field -> out == in exactly; (2) k-planes are independent: plane k of the full run
+    equals a single-plane run; (3) a 96-row slab matches the oracle bit-for-bit."""
+    ni, nj, nk = 1024, 1024, 80
+    f = gen.hdiff_inputs(ni, nj, nk, seed=42)
+    d = {k: _dev(v, (2, 2, 0)) for k, v in f.items()}
+    stencils.horizontal_diffusion(d["in_field"], d["out_field"], d["coeff"], origin=(2, 2, 0),
+                                  domain=(ni, nj, nk))
+    out = d["out_field"].asnumpy()
+    sl = (slice(0, ni + 4), slice(500, 600), slice(37, 39))
+    sub = {k: np.ascontiguousarray(v[sl]) for k, v in f.items()}
+    ref = oracle.hdiff(sub["in_field"], sub["out_field"], sub["coeff"], domain=(ni, 96, 2))
+    assert np.array_equal(out[2:-2, 502:598, 37:39], ref[2:-2, 2:-2, :])
+    assert not out[:2].any() and not out[:, -2:].any()
+    const = storage.full((ni + 4, nj + 4, 2), 3.25, backend="b200", aligned_index=(2, 2, 0))
+    o2 = storage.zeros((ni + 4, nj + 4, 2), backend="b200", aligned_index=(2, 2, 0))
+    stencils.horizontal_diffusion(const, o2, d["coeff"][:, :, :2], origin=(2, 2, 0), domain=(ni, nj, 2))
+    assert np.all(o2.asnumpy()[2:-2, 2:-2] == 3.25)
+
+
+def test_full_size_properties_vadv():
+    """1024x1024x80: columns are independent -> a strip of columns equals the oracle on that strip."""
+    ni, nj, nk = 1024, 1024, 80
+    f = gen.vadv_inputs(ni, nj, nk, seed=7)
+    out = run_vadv(f, (ni, nj, nk), 0)
+    sub = {k: (np.ascontiguousarray(v[:, 300:304]) if k != "dtr_stage" else v) for k, v in f.items()}
+    ref = oracle.vadv(sub["utens_stage"], sub["u_stage"], sub["wcon"], sub["u_pos"], sub["utens"],
+                      dtr_stage=sub["dtr_stage"], domain=(ni, 4, nk))
+    assert np.array_equal(out[:ni, 300:304], ref[:ni])
+    assert np.array_equal(out[ni], f["utens_stage"][ni])  # the i+1 halo column is not written

@@ -1,0 +1,86 @@
+#!/usr/bin/env python
+"""Kernel micro-benchmark: time the hdiff / vadv / tridiag kernel variants with CUDA events.
+
+    python tools/kbench.py --stencil hdiff --shape 1024 1024 80 --variants 1 2 3 --iters 20
+
+Inputs are resident in HBM; three buffer sets are rotated so no field can stay in the 126 MB L2.
+Prints one JSON line per variant with ms, grid-points/s and effective (algorithmic) GB/s.
+"""
+import argparse
+import json
+import os
+import sys
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from gt4py_b200 import Event, stencils, storage, synchronize  # noqa: E402
+from oracle import inputs as gen  # noqa: E402
+
+ALG_BYTES = {"hdiff": 24, "vadv": 48, "tridiag": 56}
+
+
+def make_sets(stencil, ni, nj, nk, nsets):
+    sets = []
+    if stencil == "hdiff":
+        f = gen.hdiff_inputs(ni, nj, nk)
+        for _ in range(nsets):
+            sets.append({k: storage.from_array(v, backend="b200", aligned_index=(2, 2, 0)) for k, v in f.items()})
+    elif stencil == "vadv":
+        f = gen.vadv_inputs(ni, nj, nk)
+        for _ in range(nsets):
+            sets.append({k: (storage.from_array(v, backend="b200") if k != "dtr_stage" else v) for k, v in f.items()})
+    else:
+        f = gen.tridiag_inputs(ni, nj, nk)
+        for _ in range(nsets):
+            sets.append({k: storage.from_array(v, backend="b200") for k, v in f.items()})
+    return sets
+
+
+def call(stencil, st, d, dom):
+    if stencil == "hdiff":
+        st(d["in_field"], d["out_field"], d["coeff"], origin=(2, 2, 0), domain=dom)
+    elif stencil == "vadv":
+        st(d["utens_stage"], d["u_stage"], d["wcon"], d["u_pos"], d["utens"], dtr_stage=d["dtr_stage"],
+           origin=(0, 0, 0), domain=dom)
+    else:
+        st(d["inf"], d["diag"], d["sup"], d["rhs"], d["out"], origin=(0, 0, 0), domain=dom)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--stencil", default="hdiff")
+    ap.add_argument("--shape", type=int, nargs=3, default=[1024, 1024, 80])
+    ap.add_argument("--variants", type=int, nargs="+", default=[0])
+    ap.add_argument("--iters", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--sets", type=int, default=3)
+    a = ap.parse_args()
+    ni, nj, nk = a.shape
+    dom = (ni, nj, nk)
+    cls = {"hdiff": stencils.HorizontalDiffusion, "vadv": stencils.VerticalAdvectionDycore,
+           "tridiag": stencils.TridiagonalSolver}[a.stencil]
+    sets = make_sets(a.stencil, ni, nj, nk, a.sets)
+    n = ni * nj * nk
+    for v in a.variants:
+        st = cls.with_variant(v)
+        type(st).configure(device_sync=False)
+        for it in range(a.warmup):
+            call(a.stencil, st, sets[it % a.sets], dom)
+        synchronize()
+        evs = [(Event(), Event()) for _ in range(a.iters)]
+        for it in range(a.iters):
+            evs[it][0].record()
+            call(a.stencil, st, sets[it % a.sets], dom)
+            evs[it][1].record()
+        synchronize()
+        ms = np.array([s.elapsed_ms(e) for s, e in evs])
+        best, med = float(ms.min()), float(np.median(ms))
+        print(json.dumps({"stencil": a.stencil, "shape": dom, "variant": v, "ms_min": round(best, 4),
+                          "ms_median": round(med, 4), "gpts_s_median": round(n / med / 1e6, 2),
+                          "alg_GBs_median": round(n * ALG_BYTES[a.stencil] / med / 1e6, 1),
+                          "alg_GBs_best": round(n * ALG_BYTES[a.stencil] / best / 1e6, 1)}), flush=True)
+
+
+if __name__ == "__main__":
+    main()
