@@ -191,3 +191,43 @@ int b200_launch(void *kernel, const uint32_t grid[3], const uint32_t block[3],
 }
 
 }  // extern "C"
+
+// ---- TMA tensor maps (driver entry point resolved through the runtime; libcuda is not linked) ----
+#include "tma.cuh"
+
+namespace b200 {
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+
+int encode_tmap_f64(CUtensorMap *map, const double *base, const int64_t extent[3], int64_t sj, int64_t sk,
+                    const uint32_t box[3])
+{
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        B200_CUDA_CHECK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q));
+        if (q != cudaDriverEntryPointSuccess || !p) {
+            set_error("cuTensorMapEncodeTiled is not available in this driver");
+            return B200_ECUDA;
+        }
+        fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    cuuint64_t dims[3] = {(cuuint64_t)extent[0], (cuuint64_t)extent[1], (cuuint64_t)extent[2]};
+    cuuint64_t strides[2] = {(cuuint64_t)sj * 8, (cuuint64_t)sk * 8};
+    cuuint32_t bx[3] = {box[0], box[1], box[2]};
+    cuuint32_t es[3] = {1, 1, 1};
+    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, const_cast<double *>(base), dims, strides, bx, es,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled failed with CUresult %d (extent %lld x %lld x %lld, strides %lld/%lld, "
+                  "box %u x %u x %u)", (int)r, (long long)extent[0], (long long)extent[1], (long long)extent[2],
+                  (long long)sj, (long long)sk, box[0], box[1], box[2]);
+        return B200_ECUDA;
+    }
+    return B200_OK;
+}
+}  // namespace b200

@@ -14,25 +14,9 @@
 //       fields + 1 output (48 B/point) plus the backward re-read of u_pos (normally an L2 hit).
 //   vadv_column_gmem (variant 1): same arithmetic, LIFO in a global scratch buffer; works for any
 //       nk and any strides (safe path, also the "GridTools-style" 80 B/point baseline).
-#include "common.cuh"
+#include "vadv.cuh"
 
 namespace b200 {
-
-struct VadvArgs {
-    View3<double> utens_stage;
-    View3<const double> u_stage, wcon, u_pos, utens;
-    double dtr_stage;
-    int ni, nj, nk;
-};
-
-constexpr double BET_M = 0.5, BET_P = 0.5;
-
-// One level's worth of inputs (what a forward step loads).
-struct Lvl {
-    double w0, w1;  // wcon(i, k+1), wcon(i+1, k+1)
-    double us;      // u_stage(k+1)
-    double up, ut, uts;  // u_pos(k), utens(k), utens_stage(k)
-};
 
 struct Ptrs {
     const double *__restrict__ us, *__restrict__ w0, *__restrict__ w1, *__restrict__ up,
@@ -59,60 +43,6 @@ __device__ __forceinline__ Lvl load_level(const Ptrs &p, int k, int nk)
         l.w0 = l.w1 = l.us = 0.0;
     }
     return l;
-}
-
-// Rolling state carried through the forward sweep.
-struct Fwd {
-    double us_m1, us_0;  // u_stage(k-1), u_stage(k)
-    double wsum;         // wcon(i+1,k) + wcon(i,k)
-    double ccol_m1, dcol_m1;
-};
-
-// Forward step of level k (section chosen by k).  Returns (ccol, dcol) of the level.
-__device__ __forceinline__ void forward_level(const Lvl &l, Fwd &s, double dtr, int k, int nk,
-                                              double &ccol, double &dcol)
-{
-    const double wsum_p1 = l.w1 + l.w0;  // wcon[1,0,1] + wcon[0,0,1]
-    const double us_p1 = l.us;
-    if (k == 0) {  // interval(0, 1)  :248-264
-        double gcv = 0.25 * wsum_p1;
-        double cs = gcv * BET_M;
-        double cc = gcv * BET_P;
-        double bcol = dtr - cc;
-        double correction = -cs * (us_p1 - s.us_0);
-        double dc = ((dtr * l.up + l.ut) + l.uts) + correction;
-        double divided = 1.0 / bcol;
-        ccol = cc * divided;
-        dcol = dc * divided;
-    } else if (k < nk - 1) {  // interval(1, -1)  :266-287
-        double gav = -0.25 * s.wsum;
-        double gcv = 0.25 * wsum_p1;
-        double as_ = gav * BET_M;
-        double cs = gcv * BET_M;
-        double acol = gav * BET_P;
-        double cc = gcv * BET_P;
-        double bcol = (dtr - acol) - cc;
-        double correction = -as_ * (s.us_m1 - s.us_0) - cs * (us_p1 - s.us_0);
-        double dc = ((dtr * l.up + l.ut) + l.uts) + correction;
-        double divided = 1.0 / (bcol - s.ccol_m1 * acol);
-        ccol = cc * divided;
-        dcol = (dc - s.dcol_m1 * acol) * divided;
-    } else {  // interval(-1, None)  :289-303
-        double gav = -0.25 * s.wsum;
-        double as_ = gav * BET_M;
-        double acol = gav * BET_P;
-        double bcol = dtr - acol;
-        double correction = -as_ * (s.us_m1 - s.us_0);
-        double dc = ((dtr * l.up + l.ut) + l.uts) + correction;
-        double divided = 1.0 / (bcol - s.ccol_m1 * acol);
-        ccol = s.ccol_m1;  // ccol is not assigned on the last level (unused by the backward sweep)
-        dcol = (dc - s.dcol_m1 * acol) * divided;
-    }
-    s.us_m1 = s.us_0;
-    s.us_0 = us_p1;
-    s.wsum = wsum_p1;
-    s.ccol_m1 = ccol;
-    s.dcol_m1 = dcol;
 }
 
 __device__ __forceinline__ Ptrs make_ptrs(const VadvArgs &a, int i, int j)
@@ -262,10 +192,30 @@ extern "C" int b200_vadv(const b200_field *utens_stage, const b200_field *u_stag
         B200_CUDA_CHECK(cudaGetDevice(&dev));
         B200_CUDA_CHECK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
     }
+    if (variant == 0 || variant == 7 || variant == 8) {  // TMEM-LIFO kernel, 256 columns / SM (vadv_tmem.cu)
+        bool handled = false;
+        if ((rc = launch_vadv_tmem(a, variant, stream, &handled))) return rc;
+        if (handled) return B200_OK;
+        if (variant != 0) {
+            set_error("vadv variant %d (TMEM) needs unit I stride, 16-byte aligned origins, even J/K strides "
+                      "and nk small enough for the on-chip LIFO", variant);
+            return B200_EUNSUP;
+        }
+    }
+    if (variant == 0 || (variant >= 4 && variant <= 6)) {  // TMA-fed shared-memory LIFO (vadv_tma.cu)
+        bool handled = false;
+        if ((rc = launch_vadv_tma(a, variant, stream, &handled))) return rc;
+        if (handled) return B200_OK;
+        if (variant != 0) {
+            set_error("vadv variant %d (TMA) needs unit I stride, 16-byte aligned origins, even J/K strides "
+                      "and nk small enough for the shared-memory LIFO", variant);
+            return B200_EUNSUP;
+        }
+    }
     // threads per block for the smem-LIFO kernel: as many warps as the LIFO allows, at most 5
     int warps = (int)(max_smem / ((size_t)a.nk * 16 * 32));
     if (warps > 5) warps = 5;
-    if (variant == 0) variant = warps >= 1 ? 2 : 1;
+    if (variant == 0) variant = 1;  // generic fallback: global-memory LIFO, any strides / nk
 
     if (variant == 2 || variant == 3) {
         if (warps < 1) {

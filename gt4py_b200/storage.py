@@ -242,6 +242,32 @@ class DeviceArray:
         lo, hi = self._extent()
         return lo == 0 and hi == self.nbytes
 
+    # -- asynchronous raw transfers to / from pinned host mirrors (see `pinned_like`) ------------
+    def copy_from_host(self, host: np.ndarray, stream=None):
+        """Asynchronous H2D copy of the whole byte extent from a host mirror with identical
+        shape / strides / dtype (``pinned_like(self)``).  One cudaMemcpyAsync, no staging."""
+        self._check_mirror(host)
+        lo, hi = self._extent()
+        if hi > lo:
+            _lib.check(_lib.lib().b200_memcpy_h2d(c_void_p(self.ptr + lo), c_void_p(host.ctypes.data + lo),
+                                                  hi - lo, _lib.stream_handle(stream)))
+        return self
+
+    def copy_to_host(self, host: np.ndarray, stream=None):
+        """Asynchronous D2H copy of the whole byte extent into a host mirror (``pinned_like``)."""
+        self._check_mirror(host)
+        lo, hi = self._extent()
+        if hi > lo:
+            _lib.check(_lib.lib().b200_memcpy_d2h(c_void_p(host.ctypes.data + lo), c_void_p(self.ptr + lo),
+                                                  hi - lo, _lib.stream_handle(stream)))
+        return host
+
+    def _check_mirror(self, host):
+        if not isinstance(host, np.ndarray) or host.shape != self.shape or \
+                host.strides != self.strides or host.dtype != self.dtype:
+            raise ValueError("host mirror must be a numpy array with the shape, strides and dtype of "
+                             "the device array (use gt4py_b200.storage.pinned_like)")
+
     def fill(self, value):
         if self._is_dense() and (value == 0 or self.dtype.itemsize == 1):
             byte = int(np.array(value, dtype=self.dtype).view(np.uint8)[0]) if value != 0 else 0
@@ -365,6 +391,51 @@ def from_array(data, dtype=None, *, backend: str = BACKEND_NAME, aligned_index=N
     arr = zeros(shape, dtype, backend=backend, aligned_index=aligned_index, dimensions=dimensions)
     arr.set(host)
     return arr
+
+
+class _PinnedBuffer:
+    """Owner of one cudaMallocHost allocation, exported to numpy through the buffer protocol."""
+
+    def __init__(self, nbytes: int):
+        p = c_void_p()
+        _lib.check(_lib.lib().b200_host_alloc(byref(p), max(nbytes, 1)))
+        self.ptr = p.value
+        self.nbytes = nbytes
+        import ctypes
+
+        self.array = np.ctypeslib.as_array((ctypes.c_uint8 * max(nbytes, 1)).from_address(self.ptr))
+
+    def __del__(self):
+        try:
+            if self.ptr:
+                _lib.lib().b200_host_free(c_void_p(self.ptr))
+                self.ptr = None
+        except Exception:
+            pass
+
+
+_PINNED_OWNERS = {}
+
+
+def pinned_like(array: DeviceArray, data=None) -> np.ndarray:
+    """A page-locked host mirror of `array`: a numpy array with the same shape, strides and dtype
+    (so that H2D / D2H are single contiguous copies of the byte extent), optionally filled with
+    `data`.  Pair with ``DeviceArray.copy_from_host`` / ``copy_to_host``."""
+    lo, hi = array._extent()
+    owner = _PinnedBuffer(hi - lo)
+    raw = owner.array
+    host = np.ndarray(array.shape, dtype=array.dtype, buffer=raw.data, offset=-lo, strides=array.strides)
+    _PINNED_OWNERS[host.ctypes.data] = owner  # keep the allocation alive with the process
+    if data is not None:
+        host[...] = data
+    return host
+
+
+def free_pinned(host: np.ndarray) -> None:
+    """Release a mirror returned by `pinned_like` (it must not be used afterwards)."""
+    owner = _PINNED_OWNERS.pop(host.ctypes.data, None)
+    if owner is not None:
+        owner.__del__()
 
 
 def asnumpy(array) -> np.ndarray:
