@@ -192,7 +192,7 @@ extern "C" int b200_vadv(const b200_field *utens_stage, const b200_field *u_stag
         B200_CUDA_CHECK(cudaGetDevice(&dev));
         B200_CUDA_CHECK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
     }
-    if (variant == 0 || variant == 7 || variant == 8) {  // TMEM-LIFO kernel, 256 columns / SM (vadv_tmem.cu)
+    if (variant == 0 || (variant >= 7 && variant <= 9)) {  // TMEM-LIFO kernel, 256 columns / SM (vadv_tmem.cu)
         bool handled = false;
         if ((rc = launch_vadv_tmem(a, variant, stream, &handled))) return rc;
         if (handled) return B200_OK;

@@ -141,6 +141,63 @@ __device__ __forceinline__ void rec_level(const Pre &p, double &ccol_m1, double 
     dcol_m1 = num * divided;
 }
 
+// ---- reduced-operation form of pre_level / rec_level (vadv_fused kernel) ---------------------------------
+// With BET_M = BET_P = 0.5 (the stencil's fixed externals) and power-of-two scalings being exact:
+//     cc(k)   = (0.25 * wsum(k+1)) * 0.5           == 0.125 * wsum(k+1)
+//     acol(k) = (-0.25 * wsum(k)) * 0.5            == -cc(k-1)            (as_ == acol, cs == cc)
+//     -as_ * (us(k-1) - us(k))                     == -(cc(k-1) * (us(k) - us(k-1)))  == -q(k-1)
+//      cs  * (us(k+1) - us(k))                     ==   cc(k) * d(k)                  ==  q(k)
+// so every level needs one new product q(k) = cc(k) * d(k), d(k) = us(k+1) - us(k), and reuses q(k-1).
+// All identities are exact in IEEE-754 binary64 (sign-symmetric rounding; scaling by 2^-n is exact unless
+// the result is subnormal, i.e. |wcon| < 2^-1019), so results stay bit-identical to the reference.
+struct Pre2 {
+    double ccp;   // cc(k-1) == -acol(k)
+    double cc;    // cc(k)
+    double bcol, dc;
+};
+
+struct Roll2 {
+    double us_0;   // u_stage(k)
+    double ccp;    // cc(k-1)
+    double qp;     // q(k-1) = cc(k-1) * (us(k) - us(k-1))
+};
+
+__device__ __forceinline__ Pre2 pre_level2(const Lvl &l, Roll2 &r, double dtr)
+{
+    Pre2 p;
+    p.ccp = r.ccp;
+    p.cc = 0.125 * (l.w1 + l.w0);
+    p.bcol = (dtr + r.ccp) - p.cc;                       // (dtr - acol) - ccol
+    const double q = p.cc * (l.us - r.us_0);
+    const double correction = -r.qp - q;                 // -as*(us[-1]-us) - cs*(us[+1]-us)
+    p.dc = ((dtr * l.up + l.ut) + l.uts) + correction;
+    r.us_0 = l.us;
+    r.ccp = p.cc;
+    r.qp = q;
+    return p;
+}
+
+// One step of the Thomas recurrence with the in-range reciprocal; `ok` is cleared if the divisor left
+// the range in which rcp_rn_inrange is correctly rounded (the caller then redoes the stage with `/`).
+__device__ __forceinline__ void rec_level2(const Pre2 &p, double &ccol, double &dcol, bool &ok)
+{
+    const double den = p.bcol + ccol * p.ccp;            // bcol - ccol[k-1] * acol
+    const double num = p.dc + dcol * p.ccp;              // dcol - dcol[k-1] * acol
+    ok = ok && rcp_inrange(den);
+    const double divided = rcp_rn_inrange(den);
+    ccol = p.cc * divided;
+    dcol = num * divided;
+}
+
+__device__ __forceinline__ void rec_level2_exact(const Pre2 &p, double &ccol, double &dcol)
+{
+    const double den = p.bcol + ccol * p.ccp;
+    const double num = p.dc + dcol * p.ccp;
+    const double divided = 1.0 / den;
+    ccol = p.cc * divided;
+    dcol = num * divided;
+}
+
 // host launchers (vadv_tma.cu)
 int launch_vadv_tma(const VadvArgs &a, int variant, cudaStream_t stream, bool *handled);
 // (vadv_tmem.cu)
