@@ -192,7 +192,17 @@ extern "C" int b200_vadv(const b200_field *utens_stage, const b200_field *u_stag
         B200_CUDA_CHECK(cudaGetDevice(&dev));
         B200_CUDA_CHECK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
     }
-    if (variant == 0 || (variant >= 7 && variant <= 9)) {  // TMEM-LIFO kernel, 256 columns / SM (vadv_tmem.cu)
+    if (variant == 0 || variant == 10) {  // tuned fused-sweep kernel (vadv_fused.cu)
+        bool handled = false;
+        if ((rc = launch_vadv_fused(a, stream, &handled))) return rc;
+        if (handled) return B200_OK;
+        if (variant != 0) {
+            set_error("vadv variant 10 needs unit I stride, 16-byte aligned origins, even J/K strides and nk "
+                      "small enough for the on-chip LIFO");
+            return B200_EUNSUP;
+        }
+    }
+    if (variant >= 7 && variant <= 9) {  // TMEM-LIFO kernel, 256 columns / SM (vadv_tmem.cu)
         bool handled = false;
         if ((rc = launch_vadv_tmem(a, variant, stream, &handled))) return rc;
         if (handled) return B200_OK;

@@ -1,0 +1,379 @@
+// vadv_fused.cu -- vertical advection, the tuned fast path (variant 10 and `auto`).
+//
+// Reference semantics: vertical_advection_dycore, stencil_definitions.py:235-313 (see vadv.cuh).
+//
+// Same machine mapping as vadv_tmem.cu (persistent CTA per SM, 256 columns per tile, two single-thread
+// TMA producer warps, Thomas LIFO split between Tensor Memory and shared memory) and the same fused
+// schedule as its variant 9 (the BACKWARD sweep of the previous tile runs interleaved with the FORWARD
+// sweep of the next one and hands its LIFO slots over stage by stage).  ncu showed variant 9 to be
+// instruction-issue bound (~125 warp instructions per level and column-warp, two warps per scheduler),
+// so this version is about instruction count:
+//   * the reduced-operation recurrence of vadv.cuh (pre_level2 / rec_level2: 11 + 12 fp64 operations per
+//     level instead of 22 + 14), with the branch-free in-range reciprocal and one range check per stage;
+//   * KC = 2 levels per stage, fixed: one tcgen05.st.x8 / tcgen05.ld.x8 moves both LIFO entries;
+//   * LIFO slots are addressed per stage, so the alternating stack direction costs one index computation
+//     per stage instead of per level;
+//   * the three schedules (first tile: forward only, steady state, last tile: backward only) are separate
+//     template instances instead of predicates in the loop.
+#include "vadv_tmem.cuh"
+
+namespace b200 {
+
+namespace {
+
+constexpr int FK = 2;  // levels per stage
+
+template <int TI>
+struct Fused {
+    using G = VmGeom<TI, FK>;
+
+    // per-thread state of the consumer warps
+    struct Ctx {
+        // geometry / constants
+        int t, ti, tj, lane, nk, nstages, nTs, S, SB;
+        double dtr;
+        int64_t sk;
+        uint64_t *fullF, *emptyF, *fullB, *emptyB;
+        const unsigned char *ringF, *ringB;
+        double *lifo_t;     // shared-memory part of the LIFO, this thread's column
+        uint32_t tstack;    // Tensor-Memory part of the LIFO, this thread's lane / column half
+        // ring cursors
+        int sF, sB;
+        uint32_t phF, phB;
+        // forward sweep of the new tile
+        Roll2 roll;
+        double ccol, dcol;
+        Pre2 pend[FK];
+        // backward sweep of the old tile
+        double datacol;
+        double *op;         // utens_stage(i, j, 2 * kb) of the old tile
+        bool valid_old;
+    };
+
+    __device__ static __forceinline__ void push(Ctx &c, int q, double c0, double d0, double c1, double d1)
+    {
+        if (q < c.nTs) {
+            tmem_push2(c.tstack + 8u * (uint32_t)q, c0, d0, c1, d1);
+        } else {
+            double *s = c.lifo_t + (size_t)(q - c.nTs) * 4 * VM_COLS;
+            s[0] = c0;
+            s[VM_COLS] = d0;
+            s[2 * VM_COLS] = c1;
+            s[3 * VM_COLS] = d1;
+        }
+    }
+
+    // Thomas recurrence over the pending stage; result pushed into LIFO slot q
+    __device__ static __forceinline__ void solve_push(Ctx &c, int q)
+    {
+        double cc = c.ccol, dc = c.dcol;
+        bool ok = true;
+        rec_level2(c.pend[0], cc, dc, ok);
+        const double c0 = cc, d0 = dc;
+        rec_level2(c.pend[1], cc, dc, ok);
+        if (ok) {
+            c.ccol = cc;
+            c.dcol = dc;
+            push(c, q, c0, d0, cc, dc);
+        } else {  // a divisor outside 2^-999 .. 2^999 (or not finite): IEEE division, same rounding
+            double c0e = c.ccol, d0e = c.dcol;
+            rec_level2_exact(c.pend[0], c0e, d0e);
+            double c1e = c0e, d1e = d0e;
+            rec_level2_exact(c.pend[1], c1e, d1e);
+            c.ccol = c1e;
+            c.dcol = d1e;
+            push(c, q, c0e, d0e, c1e, d1e);
+        }
+    }
+
+    template <bool FWD, bool BWD>
+    __device__ static __forceinline__ void sweep(Ctx &c, const int dir)
+    {
+        const int t = c.t;
+        const bool pad_top = (c.nk & 1) != 0;  // level 2*nstages-1 does not exist
+        int qprev = 0;
+#pragma unroll 1
+        for (int ks = 0; ks < c.nstages; ++ks) {
+            const int q = dir ? c.nstages - 1 - ks : ks;  // LIFO slot popped now, refilled next iteration
+            const bool tm = q < c.nTs;
+            Raw8 raw;
+            double cc0, dc0, cc1, dc1;
+            if (BWD) {
+                if (tm) {
+                    tmem_pop2_issue(c.tstack + 8u * (uint32_t)q, raw);
+                } else {
+                    const double *s = c.lifo_t + (size_t)(q - c.nTs) * 4 * VM_COLS;
+                    cc0 = s[0];
+                    dc0 = s[VM_COLS];
+                    cc1 = s[2 * VM_COLS];
+                    dc1 = s[3 * VM_COLS];
+                }
+            }
+            if (FWD) {
+                mbar_wait(&c.fullF[c.sF], c.phF);
+                const double *slot = reinterpret_cast<const double *>(c.ringF + (size_t)c.sF * G::SLOT_F) + t;
+                const double *w = slot - t + 4 * FK * VM_COLS + c.tj * G::WROW + c.ti;
+                Lvl l[FK];
+#pragma unroll
+                for (int u = 0; u < FK; ++u) {
+                    l[u].us = slot[u * VM_COLS];
+                    l[u].up = slot[(FK + u) * VM_COLS];
+                    l[u].ut = slot[(2 * FK + u) * VM_COLS];
+                    l[u].uts = slot[(3 * FK + u) * VM_COLS];
+                    l[u].w0 = w[u * G::WLVL];
+                    l[u].w1 = w[u * G::WLVL + 1];
+                }
+                __syncwarp();
+                if (c.lane == 0) mbar_arrive(&c.emptyF[c.sF]);
+                if (++c.sF == c.S) { c.sF = 0; c.phF ^= 1; }
+                if (ks > 0) solve_push(c, qprev);
+#pragma unroll
+                for (int u = 0; u < FK; ++u) c.pend[u] = pre_level2(l[u], c.roll, c.dtr);
+            }
+            if (BWD) {
+                mbar_wait(&c.fullB[c.sB], c.phB);
+                const double *slot = reinterpret_cast<const double *>(c.ringB + (size_t)c.sB * G::SLOT_B) + t;
+                const double up0 = slot[0], up1 = slot[VM_COLS];
+                __syncwarp();
+                if (c.lane == 0) mbar_arrive(&c.emptyB[c.sB]);
+                if (++c.sB == c.SB) { c.sB = 0; c.phB ^= 1; }
+                if (tm) {
+                    tmem_pop2_wait(raw);
+                    cc0 = __hiloint2double((int)raw.r[1], (int)raw.r[0]);
+                    dc0 = __hiloint2double((int)raw.r[3], (int)raw.r[2]);
+                    cc1 = __hiloint2double((int)raw.r[5], (int)raw.r[4]);
+                    dc1 = __hiloint2double((int)raw.r[7], (int)raw.r[6]);
+                }
+                // levels 2*kb+1 then 2*kb of the old tile (kb = nstages-1-ks)  :305-312
+                if (!(ks == 0 && pad_top)) {
+                    c.datacol = dc1 - cc1 * c.datacol;
+                    if (c.valid_old) __stcs(c.op + c.sk, c.dtr * (c.datacol - up1));
+                }
+                c.datacol = dc0 - cc0 * c.datacol;
+                if (c.valid_old) __stcs(c.op, c.dtr * (c.datacol - up0));
+                c.op -= 2 * c.sk;
+            }
+            qprev = q;
+        }
+        if (FWD) solve_push(c, qprev);
+    }
+};
+
+}  // namespace
+
+template <int TI>
+__global__ void __launch_bounds__(VM_THREADS, 1)
+vadv_fused2_kernel(VadvArgs a, const __grid_constant__ CUtensorMap m_us, const __grid_constant__ CUtensorMap m_w,
+                   const __grid_constant__ CUtensorMap m_up, const __grid_constant__ CUtensorMap m_ut,
+                   const __grid_constant__ CUtensorMap m_uts, int S, int SB, int nTs, int tiles_i, int ntiles)
+{
+    using F = Fused<TI>;
+    using G = typename F::G;
+    extern __shared__ __align__(1024) unsigned char smem[];
+    uint64_t *fullF = reinterpret_cast<uint64_t *>(smem);
+    uint64_t *emptyF = fullF + VM_MAX_STAGES;
+    uint64_t *fullB = emptyF + VM_MAX_STAGES;
+    uint64_t *emptyB = fullB + VM_MAX_STAGES;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(emptyB + VM_MAX_STAGES);
+    unsigned char *ringF = smem + VM_BAR_BYTES;
+    unsigned char *ringB = ringF + (size_t)S * G::SLOT_F;
+    double *lifo = reinterpret_cast<double *>(ringB + (size_t)SB * G::SLOT_B);  // stage slots [nTs, nstages)
+
+    const int nk = a.nk;
+    const int nstages = (nk + FK - 1) / FK;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < S; ++s) {
+            mbar_init(&fullF[s], 1);
+            mbar_init(&emptyF[s], VM_CWARPS);
+        }
+        for (int s = 0; s < SB; ++s) {
+            mbar_init(&fullB[s], 1);
+            mbar_init(&emptyB[s], VM_CWARPS);
+        }
+        mbar_fence_init();
+    }
+    if (warp == VM_CWARPS) tmem_alloc(tmem_slot, VM_TMEM_COLS);
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == VM_CWARPS) {
+        // ================= forward-ring producer: one thread issues the TMA loads =====================
+        if (lane == 0) {
+            tma_prefetch_desc(&m_us);
+            tma_prefetch_desc(&m_w);
+            tma_prefetch_desc(&m_up);
+            tma_prefetch_desc(&m_ut);
+            tma_prefetch_desc(&m_uts);
+            int sF = 0;
+            uint32_t phF = 0;
+            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+                const int ci = (tile % tiles_i) * TI, cj = (tile / tiles_i) * G::TJ;
+                for (int ks = 0; ks < nstages; ++ks) {
+                    mbar_wait(&emptyF[sF], phF ^ 1);
+                    mbar_expect_tx(&fullF[sF], G::TX_F);
+                    unsigned char *slot = ringF + (size_t)sF * G::SLOT_F;
+                    const int k0 = ks * FK;
+                    tma_load_3d(slot, &m_us, ci, cj, k0 + 1, &fullF[sF], L2_EVICT_FIRST);
+                    tma_load_3d(slot + G::F_BYTES, &m_up, ci, cj, k0, &fullF[sF], L2_EVICT_LAST);
+                    tma_load_3d(slot + 2 * G::F_BYTES, &m_ut, ci, cj, k0, &fullF[sF], L2_EVICT_FIRST);
+                    tma_load_3d(slot + 3 * G::F_BYTES, &m_uts, ci, cj, k0, &fullF[sF], L2_EVICT_FIRST);
+                    tma_load_3d(slot + 4 * G::F_BYTES, &m_w, ci, cj, k0 + 1, &fullF[sF], L2_EVICT_FIRST);
+                    if (++sF == S) { sF = 0; phF ^= 1; }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == VM_CWARPS + 1) {
+        // ================= backward-ring producer: u_pos stages, top stage first ========================
+        if (lane == 0) {
+            int sB = 0;
+            uint32_t phB = 0;
+            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+                const int ci = (tile % tiles_i) * TI, cj = (tile / tiles_i) * G::TJ;
+                for (int ks = nstages - 1; ks >= 0; --ks) {
+                    mbar_wait(&emptyB[sB], phB ^ 1);
+                    mbar_expect_tx(&fullB[sB], G::TX_B);
+                    tma_load_3d(ringB + (size_t)sB * G::SLOT_B, &m_up, ci, cj, ks * FK, &fullB[sB], L2_EVICT_FIRST);
+                    if (++sB == SB) { sB = 0; phB ^= 1; }
+                }
+            }
+        }
+        __syncwarp();
+    } else {
+        // =========================== consumers: one column per thread ===============================
+        typename F::Ctx c;
+        c.t = threadIdx.x;
+        c.ti = c.t % TI;
+        c.tj = c.t / TI;
+        c.lane = lane;
+        c.nk = nk;
+        c.nstages = nstages;
+        c.nTs = nTs;
+        c.S = S;
+        c.SB = SB;
+        c.dtr = a.dtr_stage;
+        c.sk = a.utens_stage.sk;
+        c.fullF = fullF;
+        c.emptyF = emptyF;
+        c.fullB = fullB;
+        c.emptyB = emptyB;
+        c.ringF = ringF;
+        c.ringB = ringB;
+        c.lifo_t = lifo + c.t;
+        c.tstack = tmem_base + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)(warp >> 2) * 256u;
+        c.sF = c.sB = 0;
+        c.phF = c.phB = 0;
+        c.op = nullptr;
+        c.valid_old = false;
+        c.datacol = 0.0;
+
+        auto first_ustage = [&](int tile) -> double {
+            if (tile >= ntiles) return 0.0;
+            const int i = (tile % tiles_i) * TI + c.ti, j = (tile / tiles_i) * G::TJ + c.tj;
+            if (i >= a.ni || j >= a.nj) return 0.0;
+            return __ldg(a.u_stage.p + i + (int64_t)j * a.u_stage.sj);
+        };
+        const int my_tiles = (int)blockIdx.x < ntiles ? (ntiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+        double us0_next = first_ustage(blockIdx.x);
+
+        for (int n = 0; n <= my_tiles && my_tiles > 0; ++n) {
+            const int tile = blockIdx.x + n * gridDim.x;
+            const int dir = n & 1;  // stack direction of the tile in its forward sweep
+            c.roll.us_0 = us0_next;
+            c.roll.ccp = 0.0;
+            c.roll.qp = 0.0;
+            c.ccol = c.dcol = 0.0;
+            c.datacol = 0.0;
+            if (n < my_tiles) us0_next = first_ustage(tile + gridDim.x);
+            if (n == 0)
+                F::template sweep<true, false>(c, dir);
+            else if (n < my_tiles)
+                F::template sweep<true, true>(c, dir);
+            else
+                F::template sweep<false, true>(c, dir);
+            if (n < my_tiles) {  // this tile is the "old" one of the next round
+                const int i = (tile % tiles_i) * TI + c.ti, j = (tile / tiles_i) * G::TJ + c.tj;
+                c.valid_old = i < a.ni && j < a.nj;
+                c.op = a.utens_stage.p + i + (int64_t)j * a.utens_stage.sj + (int64_t)(nstages - 1) * FK * c.sk;
+            }
+            tmem_push_wait();
+        }
+    }
+
+    // every warp arrives here; TMEM is released only after all consumers finished their last pop
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == VM_CWARPS) tmem_dealloc(tmem_base, VM_TMEM_COLS);
+}
+
+template <int TI>
+static int launch_fused2(const VadvArgs &a, cudaStream_t stream, bool *handled)
+{
+    using G = VmGeom<TI, FK>;
+    static int max_smem = -1, sms = -1;
+    if (max_smem < 0) {
+        int dev = 0;
+        B200_CUDA_CHECK(cudaGetDevice(&dev));
+        B200_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        B200_CUDA_CHECK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+    }
+    static const int env_s = env_int("B200_VADV_STAGES", 0);
+    static const int env_sb = env_int("B200_VADV_BSTAGES", 0);
+    const int nstages = (a.nk + FK - 1) / FK;
+    const int tmem_slots = VM_TMEM_LEVELS / FK;  // 32 stage slots of 8 columns per thread
+    const int nTs = nstages < tmem_slots ? nstages : tmem_slots;
+    const size_t lifo = (size_t)(nstages - nTs) * 2 * FK * VM_COLS * 8;
+    int SB = env_sb > 0 ? env_sb : 6;
+    if (SB > VM_MAX_STAGES) SB = VM_MAX_STAGES;
+    long avail = (long)max_smem - VM_BAR_BYTES - (long)lifo;
+    while (SB > 2 && (long)SB * G::SLOT_B > avail / 4) --SB;
+    avail -= (long)SB * G::SLOT_B;
+    int S = avail > 0 ? (int)(avail / G::SLOT_F) : 0;
+    const int want = env_s > 0 ? env_s : 5;
+    if (S > want) S = want;
+    if (S > VM_MAX_STAGES) S = VM_MAX_STAGES;
+    if (S < 2) return B200_OK;  // LIFO does not fit on chip: not handled here
+    const size_t smem = VM_BAR_BYTES + (size_t)S * G::SLOT_F + (size_t)SB * G::SLOT_B + lifo;
+
+    CUtensorMap m_us, m_w, m_up, m_ut, m_uts;
+    const int64_t ext[3] = {a.ni, a.nj, a.nk}, extw[3] = {a.ni + 1, a.nj, a.nk};
+    const uint32_t box[3] = {TI, (uint32_t)G::TJ, FK}, boxw[3] = {TI + 2, (uint32_t)G::TJ, FK};
+    int rc;
+    if ((rc = encode_tmap_f64(&m_us, a.u_stage.p, ext, a.u_stage.sj, a.u_stage.sk, box))) return rc;
+    if ((rc = encode_tmap_f64(&m_w, a.wcon.p, extw, a.wcon.sj, a.wcon.sk, boxw))) return rc;
+    if ((rc = encode_tmap_f64(&m_up, a.u_pos.p, ext, a.u_pos.sj, a.u_pos.sk, box))) return rc;
+    if ((rc = encode_tmap_f64(&m_ut, a.utens.p, ext, a.utens.sj, a.utens.sk, box))) return rc;
+    if ((rc = encode_tmap_f64(&m_uts, a.utens_stage.p, ext, a.utens_stage.sj, a.utens_stage.sk, box))) return rc;
+
+    const int tiles_i = (a.ni + TI - 1) / TI, tiles_j = (a.nj + G::TJ - 1) / G::TJ;
+    const int ntiles = tiles_i * tiles_j;
+    const int grid = ntiles < sms ? ntiles : sms;
+    auto kern = vadv_fused2_kernel<TI>;
+    B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<grid, VM_THREADS, smem, stream>>>(a, m_us, m_w, m_up, m_ut, m_uts, S, SB, nTs, tiles_i, ntiles);
+    B200_CUDA_CHECK(cudaGetLastError());
+    *handled = true;
+    return B200_OK;
+}
+
+// Launch the tuned fused kernel if the layout allows it (same preconditions as vadv_tma.cu); *handled =
+// false with B200_OK means "use another variant".
+int launch_vadv_fused(const VadvArgs &a, cudaStream_t stream, bool *handled)
+{
+    *handled = false;
+    if (!tma_compatible(a.u_stage.p, a.u_stage.si, a.u_stage.sj, a.u_stage.sk) ||
+        !tma_compatible(a.wcon.p, a.wcon.si, a.wcon.sj, a.wcon.sk) ||
+        !tma_compatible(a.u_pos.p, a.u_pos.si, a.u_pos.sj, a.u_pos.sk) ||
+        !tma_compatible(a.utens.p, a.utens.si, a.utens.sj, a.utens.sk) ||
+        !tma_compatible(a.utens_stage.p, a.utens_stage.si, a.utens_stage.sj, a.utens_stage.sk))
+        return B200_OK;
+    return a.ni > 64 ? launch_fused2<128>(a, stream, handled)
+         : a.ni > 32 ? launch_fused2<64>(a, stream, handled)
+                     : launch_fused2<32>(a, stream, handled);
+}
+
+}  // namespace b200
