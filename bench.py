@@ -49,7 +49,7 @@ UNIT = "grid-points/s"
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--domain", type=int, nargs=3, default=[1024, 1024, 80],
@@ -72,7 +72,8 @@ def peaks():
 
 
 def workload_name(dom):
-    return f"hdiff + vadv at {dom[0]}x{dom[1]}x{dom[2]} float64 per GPU (BASELINE configs[2])"
+    tag = " (BASELINE configs[2])" if tuple(dom) == (1024, 1024, 80) else ""
+    return f"hdiff + vadv at {dom[0]}x{dom[1]}x{dom[2]} float64 per GPU{tag}"
 
 
 # ---- host-side synthetic inputs in the device layout (I contiguous) --------------------------------
@@ -102,7 +103,7 @@ class ClockSampler:
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--id={index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                 "-lms", "20"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._pump, daemon=True)
             self.thread.start()
         except Exception:
@@ -121,9 +122,11 @@ class ClockSampler:
             self.proc.wait(timeout=2)
         except Exception:
             self.proc.kill()
-        rows = [r for (t, r) in self.rows if (t0 is None or t >= t0 - 0.05) and (t1 is None or t <= t1 + 0.15)]
-        if not rows:
+        rows = [r for (t, r) in self.rows if (t0 is None or t >= t0) and (t1 is None or t <= t1 + 0.02)]
+        window = "timed region"
+        if not rows:  # timed region shorter than the sampling period: fall back to warm-up + timed region
             rows = [r for _, r in self.rows]
+            window = "warm-up + timed region"
         sm, mx, pw, reasons = [], [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for r in rows:
@@ -140,7 +143,7 @@ class ClockSampler:
         return {"sm_mhz": float(np.median(sm)) if sm else None,
                 "sm_max_mhz": float(max(mx)) if mx else None,
                 "power_w_max": float(max(pw)) if pw else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+                "samples": len(sm), "window": window, "reasons": sorted(reasons)}
 
 
 # ---- CPU leg (oracle port; the reference's numpy backend cannot travel to the GPU box) ---------------
@@ -281,11 +284,16 @@ def run_b200(args):
         if ev is not None:
             ev[2].record(stream)
 
+    sampler = ClockSampler(local) if rank == 0 else None
     with gb.use_stream(stream):
         for i in range(max(args.warmup, 3)):
             step(i)
         barrier()
-        sampler = ClockSampler(local) if rank == 0 else None
+        if sampler is not None:  # nvidia-smi needs a moment to start; keep the GPU busy meanwhile
+            t_s = time.perf_counter()
+            while not sampler.rows and time.perf_counter() - t_s < 3.0:
+                step(0)
+                stream.synchronize()
         evs = [(gb.Event(), gb.Event(), gb.Event()) for _ in range(args.steps)]
         e0, e1 = gb.Event(), gb.Event()
         barrier()
@@ -312,7 +320,7 @@ def run_b200(args):
                 "traffic": TRAFFIC.get(name), "ms_per_launch": round(t_ms, 4),
                 "alg_bytes_per_launch": n * ALG_BYTES[name], "peak_source": peak_src}
 
-    kernels = {"hdiff": roof("hdiff", t_h, "hdiff_jmarch"), "vadv": roof("vadv", t_v, "vadv_column")}
+    kernels = {"hdiff": roof("hdiff", t_h, "hdiff_jmarch"), "vadv": roof("vadv", t_v, "vadv_fused2_kernel")}
     dominant = "vadv" if t_v >= t_h else "hdiff"
 
     # ---- e2e: host buffers in, host buffers out, every step (public API) ----------------------------
