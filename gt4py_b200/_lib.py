@@ -35,6 +35,34 @@ class B200Error(RuntimeError):
         self.code = code
 
 
+class HaloBox(Structure):
+    """struct b200_halo_box"""
+
+    _fields_ = [
+        ("src", c_void_p),
+        ("dst", c_void_p),
+        ("src_stride", c_int64 * 3),
+        ("dst_stride", c_int64 * 3),
+        ("extent", c_int32 * 3),
+        ("reserved", c_int32),
+    ]
+
+
+HALO_MAX_PEERS = 8
+
+
+class HaloSync(Structure):
+    """struct b200_halo_sync"""
+
+    _fields_ = [
+        ("post_ready", c_void_p * HALO_MAX_PEERS),
+        ("post_done", c_void_p * HALO_MAX_PEERS),
+        ("wait_ready", c_void_p * HALO_MAX_PEERS),
+        ("wait_done", c_void_p * HALO_MAX_PEERS),
+        ("npeers", c_int32),
+    ]
+
+
 class Field(Structure):
     """struct b200_field"""
 
@@ -81,6 +109,11 @@ _PROTOTYPES = {
     "b200_hdiff": ([POINTER(Field), POINTER(Field), POINTER(Field), POINTER(c_int64), c_int, c_int, _VP], c_int),
     "b200_vadv": ([POINTER(Field)] * 5 + [c_double, POINTER(c_int64), c_int, _VP], c_int),
     "b200_tridiag": ([POINTER(Field)] * 5 + [POINTER(c_int64), c_int, _VP], c_int),
+    "b200_ipc_get_mem_handle": ([_VP, _VP], c_int),
+    "b200_ipc_open_mem_handle": ([_VP, POINTER(_VP)], c_int),
+    "b200_ipc_close_mem_handle": ([_VP], c_int),
+    "b200_halo_refresh": ([_VP, c_int, c_int, POINTER(HaloSync), ctypes.c_uint64, _VP, c_int, _VP], c_int),
+    "b200_halo_wait_done": ([POINTER(HaloSync), ctypes.c_uint64, _VP], c_int),
     "b200_module_load": ([_VP, c_size_t, POINTER(_VP)], c_int),
     "b200_module_unload": ([_VP], c_int),
     "b200_module_get_kernel": ([_VP, c_char_p, POINTER(_VP)], c_int),

@@ -135,6 +135,39 @@ B200_API int b200_kernel_set_smem(void *kernel, int dynamic_smem_bytes);
 B200_API int b200_launch(void *kernel, const uint32_t grid[3], const uint32_t block[3],
                 uint32_t dynamic_smem_bytes, void *stream, void **args, int nargs);
 
+/* ---- multi-GPU halo refresh over NVLink peer memory (csrc/halo.cu) ------------------------------
+ * New functionality: the reference has no distributed layer.  One process per GPU;
+ * a rank maps its neighbours' field allocations with CUDA IPC and pulls the halo boxes with one kernel.
+ * Ordering between ranks: step-numbered ready / done flags in peer-visible memory (see halo.cu). */
+typedef struct b200_halo_box {
+    const double *src;      /* first element of the box in the neighbour's (mapped) memory */
+    double *dst;            /* first element of the box in the local halo */
+    int64_t src_stride[3];  /* element strides I, J, K */
+    int64_t dst_stride[3];
+    int32_t extent[3];
+    int32_t reserved;
+} b200_halo_box;
+
+#define B200_HALO_MAX_PEERS 8
+typedef struct b200_halo_sync {
+    uint64_t *post_ready[B200_HALO_MAX_PEERS]; /* slot in peer p's flag block that this rank writes */
+    uint64_t *post_done[B200_HALO_MAX_PEERS];
+    const uint64_t *wait_ready[B200_HALO_MAX_PEERS]; /* local slot that peer p writes */
+    const uint64_t *wait_done[B200_HALO_MAX_PEERS];
+    int32_t npeers;
+} b200_halo_sync;
+
+B200_API int b200_ipc_get_mem_handle(void *dptr, unsigned char handle[64]);
+B200_API int b200_ipc_open_mem_handle(const unsigned char handle[64], void **dptr);
+B200_API int b200_ipc_close_mem_handle(void *dptr);
+/* boxes_dev: device array of nboxes boxes.  use_flags = 0 skips the inter-rank protocol (single-process
+ * tests, or when the caller orders ranks itself).  arrive_dev: zero-initialised device counter. */
+B200_API int b200_halo_refresh(const b200_halo_box *boxes_dev, int nboxes, int blocks_per_box,
+                      const b200_halo_sync *sync, uint64_t step, unsigned int *arrive_dev,
+                      int use_flags, void *stream);
+/* Block `stream` until every neighbour has finished pulling step `step` out of this rank's fields. */
+B200_API int b200_halo_wait_done(const b200_halo_sync *sync, uint64_t step, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -169,3 +169,56 @@ def test_full_size_properties_vadv():
                       dtr_stage=sub["dtr_stage"], domain=(ni, 4, nk))
     assert np.array_equal(out[:ni, 300:304], ref[:ni])
     assert np.array_equal(out[ni], f["utens_stage"][ni])  # the i+1 halo column is not written
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_halo_refresh_single_device_emulation(world):
+    """All ranks of a Px x Py decomposition emulated in this process on one device (no flags, host
+    ordering): the pull kernel must restore stale halos so that the decomposed hdiff / vadv equal the
+    single-domain oracle bit-for-bit."""
+    from gt4py_b200.halo import Decomposition, HaloExchanger
+    from tests import halo_helpers as hh
+
+    dom = (40, 24, 6)
+    ni, nj, nk = dom
+    decs = [Decomposition.create(world, r) for r in range(world)]
+    G = hh.global_field(world, dom, 2, seed=11)
+    gdom = (decs[0].px_count * ni, decs[0].py_count * nj, nk)
+    Gout = np.zeros_like(G)
+    oracle.hdiff(G, Gout, np.full_like(G, 0.025), origin=(2, 2, 0), domain=gdom)
+    rng = np.random.default_rng(12)
+    gshape = (gdom[0] + 1, gdom[1], nk)
+    F = {k: rng.uniform(-1, 1, gshape) for k in ("utens_stage", "u_stage", "u_pos", "utens")}
+    F["wcon"] = rng.uniform(-0.1, 0.1, gshape)
+    Vref = F["utens_stage"].copy()
+    oracle.vadv(Vref, F["u_stage"], F["wcon"], F["u_pos"], F["utens"], dtr_stage=0.15, domain=gdom)
+
+    exs, dev = [], []
+    for d in decs:
+        x, y = d.coords
+        loc = hh.local_block(G, d, dom, 2)
+        from gt4py_b200.halo import halo_boxes
+        for b in halo_boxes(d, (2, 2, 0), dom, ((2, 2), (2, 2))):
+            loc[hh.box_slices(b.dst_start, b.extent)] = -99.0
+        L = {k: v[x * ni: x * ni + ni + 1, y * nj: (y + 1) * nj].copy() for k, v in F.items()}
+        if d.neighbour(1, 0) is not None:
+            L["wcon"][ni] = 1e9
+        fields = {"in_field": _dev(loc, (2, 2, 0)), "out_field": _dev(np.zeros_like(loc), (2, 2, 0)),
+                  "coeff": _dev(np.full_like(loc, 0.025), (2, 2, 0))}
+        fields.update({k: _dev(v, (0, 0, 0)) for k, v in L.items()})
+        ex = HaloExchanger(None, d, use_flags=False)
+        ex.add_group([(fields["in_field"], (2, 2, 0), dom, ((2, 2), (2, 2))),
+                      (fields["wcon"], (0, 0, 0), dom, ((0, 1), (0, 0)))])
+        exs.append(ex)
+        dev.append(fields)
+    HaloExchanger.finalize_local(exs)
+    for ex in exs:
+        ex.refresh(0)
+    gb.synchronize()
+    for d, f in zip(decs, dev):
+        x, y = d.coords
+        stencils.horizontal_diffusion(f["in_field"], f["out_field"], f["coeff"], origin=(2, 2, 0), domain=dom)
+        stencils.vertical_advection_dycore(f["utens_stage"], f["u_stage"], f["wcon"], f["u_pos"], f["utens"],
+                                           dtr_stage=0.15, origin=(0, 0, 0), domain=dom)
+        assert np.array_equal(f["out_field"].asnumpy()[2:-2, 2:-2], hh.local_block(Gout, d, dom, 2)[2:-2, 2:-2])
+        assert np.array_equal(f["utens_stage"].asnumpy()[:ni], Vref[x * ni: (x + 1) * ni, y * nj: (y + 1) * nj])
