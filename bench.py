@@ -57,8 +57,9 @@ def parse_args():
     ap.add_argument("--sets", type=int, default=3, help="field sets rotated between steps")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--halo-mode", default="p2p", choices=["p2p", "nccl"],
-                    help="N>1: halo refresh by peer-memory pull kernels (p2p) or NCCL send/recv")
+    ap.add_argument("--halo-mode", default="push", choices=["push", "pull"],
+                    help="N>1: halo refresh by pushing faces into the neighbours' staging buffers (2 kernels) "
+                         "or by pulling boxes out of the neighbours' fields (1 kernel); both over NVLink peer memory")
     return ap.parse_args()
 
 
@@ -180,6 +181,7 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
+    os.environ["OMP_NUM_THREADS"] = str(host_threads())  # torchrun pins it to 1; the CPU arm uses every core
     dom = tuple(args.domain)
     n = dom[0] * dom[1] * dom[2]
     hin, vin = make_host_inputs(dom)
@@ -270,9 +272,9 @@ def run_b200(args):
 
     stream = gb.Stream()
 
-    def step(i, ev=None):
+    def step(i, ev=None, refresh=True):
         h, v = hsets[i % args.sets], vsets[i % args.sets]
-        if halo is not None:
+        if halo is not None and refresh:  # every rank must call refresh the same number of times
             halo.refresh(i % args.sets, stream)
         if ev is not None:
             ev[0].record(stream)
@@ -292,7 +294,7 @@ def run_b200(args):
         if sampler is not None:  # nvidia-smi needs a moment to start; keep the GPU busy meanwhile
             t_s = time.perf_counter()
             while not sampler.rows and time.perf_counter() - t_s < 3.0:
-                step(0)
+                step(0, refresh=False)
                 stream.synchronize()
         evs = [(gb.Event(), gb.Event(), gb.Event()) for _ in range(args.steps)]
         e0, e1 = gb.Event(), gb.Event()
@@ -326,7 +328,7 @@ def run_b200(args):
     # ---- e2e: host buffers in, host buffers out, every step (public API) ----------------------------
     e2e = None
     if not args.no_e2e:
-        e2e = run_e2e(gb, storage, hd, va, hsets[0], vsets[0], hin, vin, dom, dtr, args, barrier, allmax, world)
+        e2e = run_e2e(gb, storage, hd, va, hsets[0], vsets[0], hin, vin, dom, dtr, args, barrier, allmax, world, halo)
 
     # ---- CPU baseline (rank 0, N == 1 only) ---------------------------------------------------------
     cpu = None
@@ -373,7 +375,7 @@ def decomposition(world):
     return {1: "1x1", 2: "2x1", 4: "2x2", 8: "4x2"}.get(world, f"{world}x1") + " (IxJ ranks)"
 
 
-def run_e2e(gb, storage, hd, va, h, v, hin, vin, dom, dtr, args, barrier, allmax, world):
+def run_e2e(gb, storage, hd, va, h, v, hin, vin, dom, dtr, args, barrier, allmax, world, halo=None):
     """Host buffers -> device -> kernels -> host buffers, all inside the timed region."""
     n = dom[0] * dom[1] * dom[2]
     pin_h = {k: storage.pinned_like(h[k], hin[k]) for k in h}
@@ -386,9 +388,12 @@ def run_e2e(gb, storage, hd, va, h, v, hin, vin, dom, dtr, args, barrier, allmax
         b_in = b_out = 0
         for k in ("in_field", "coeff"):
             h[k].copy_from_host(pin_h[k], stream); b_in += pin_h[k].nbytes
+        v["wcon"].copy_from_host(pin_v["wcon"], stream); b_in += pin_v["wcon"].nbytes
+        if halo is not None:
+            halo.refresh(0, stream)
         hd(h["in_field"], h["out_field"], h["coeff"], origin=(2, 2, 0), domain=dom)
         h["out_field"].copy_to_host(pin_h["out_field"], stream); b_out += pin_h["out_field"].nbytes
-        for k in ("utens_stage", "u_stage", "wcon", "u_pos", "utens"):
+        for k in ("utens_stage", "u_stage", "u_pos", "utens"):
             v[k].copy_from_host(pin_v[k], stream); b_in += pin_v[k].nbytes
         va(v["utens_stage"], v["u_stage"], v["wcon"], v["u_pos"], v["utens"], dtr_stage=dtr,
            origin=(0, 0, 0), domain=dom)

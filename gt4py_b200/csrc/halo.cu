@@ -52,17 +52,25 @@ __device__ __forceinline__ unsigned long long read_flag(const unsigned long long
 }
 
 // grid = (blocks per box, nboxes).  *arrive (device counter, zero between launches) lets the last block
-// post the done flags after every block finished copying.
+// post flags after every block finished copying.  mode:
+//   0  plain box copy, no inter-rank protocol
+//   1  PULL : post ready(s), wait neighbours' ready(s), copy (src = peer memory), post done(s)
+//   2  PUSH : copy (dst = the neighbour's contiguous staging buffer), then post ready(s)
+//   3  UNPACK: wait neighbours' ready(s), copy (local staging -> halo cells)
+// PUSH + UNPACK is the fast path: boundary faces are only 2 elements wide along the contiguous axis, and
+// 16-byte peer LOADS are bound by NVLink round-trip latency x outstanding requests, while the pushed stores
+// are posted writes, coalesced because the staging buffer is contiguous.
 __global__ void __launch_bounds__(256)
 halo_refresh_kernel(const HaloBox *__restrict__ boxes, HaloSync sync, unsigned long long step,
                     unsigned int *arrive, int use_flags)
 {
-    if (use_flags) {
+    const int mode = use_flags;
+    if (mode == 1 || mode == 3) {
         if (threadIdx.x == 0) {
-            if (blockIdx.x == 0 && blockIdx.y == 0)
+            if (mode == 1 && blockIdx.x == 0 && blockIdx.y == 0)
                 for (int p = 0; p < sync.npeers; ++p) post_flag(sync.post_ready[p], step);
             for (int p = 0; p < sync.npeers; ++p)
-                while (read_flag(sync.wait_ready[p]) < step) __nanosleep(64);
+                while (read_flag(sync.wait_ready[p]) < step) __nanosleep(32);
         }
         __syncthreads();
     }
@@ -72,36 +80,54 @@ halo_refresh_kernel(const HaloBox *__restrict__ boxes, HaloSync sync, unsigned l
     if ((b.n[0] & 1) == 0 && b.ss[0] == 1 && b.ds[0] == 1 &&
         ((reinterpret_cast<uintptr_t>(b.src) | reinterpret_cast<uintptr_t>(b.dst)) & 15) == 0 &&
         ((b.ss[1] | b.ss[2] | b.ds[1] | b.ds[2]) & 1) == 0) {
-        // 128-bit path: pairs along the contiguous axis
+        // 128-bit path: pairs along the contiguous axis; two independent peer loads in flight per thread
         const int half = b.n[0] >> 1;
         const int64_t npairs = (int64_t)half * rows;
-        for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < npairs;
-             idx += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+        auto src_of = [&](int64_t idx) {
             const int i2 = (int)(idx % half);
             const int64_t r = idx / half;
-            const int j = (int)(r % b.n[1]);
-            const int k = (int)(r / b.n[1]);
-            const double2 v = *reinterpret_cast<const double2 *>(b.src + 2 * i2 + j * b.ss[1] + k * b.ss[2]);
-            *reinterpret_cast<double2 *>(b.dst + 2 * i2 + j * b.ds[1] + k * b.ds[2]) = v;
+            return b.src + 2 * i2 + (r % b.n[1]) * b.ss[1] + (r / b.n[1]) * b.ss[2];
+        };
+        auto dst_of = [&](int64_t idx) {
+            const int i2 = (int)(idx % half);
+            const int64_t r = idx / half;
+            return b.dst + 2 * i2 + (r % b.n[1]) * b.ds[1] + (r / b.n[1]) * b.ds[2];
+        };
+        for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < npairs; idx += 2 * stride) {
+            const int64_t idx2 = idx + stride;
+            const double2 v0 = *reinterpret_cast<const double2 *>(src_of(idx));
+            double2 v1 = make_double2(0.0, 0.0);
+            if (idx2 < npairs) v1 = *reinterpret_cast<const double2 *>(src_of(idx2));
+            *reinterpret_cast<double2 *>(dst_of(idx)) = v0;
+            if (idx2 < npairs) *reinterpret_cast<double2 *>(dst_of(idx2)) = v1;
         }
     } else {
-        for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
-             idx += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+        auto off = [&](int64_t idx, const int64_t (&st)[3]) {
             const int i = (int)(idx % b.n[0]);
             const int64_t r = idx / b.n[0];
-            const int j = (int)(r % b.n[1]);
-            const int k = (int)(r / b.n[1]);
-            b.dst[i * b.ds[0] + j * b.ds[1] + k * b.ds[2]] = b.src[i * b.ss[0] + j * b.ss[1] + k * b.ss[2]];
+            return i * st[0] + (r % b.n[1]) * st[1] + (r / b.n[1]) * st[2];
+        };
+        for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += 2 * stride) {
+            const int64_t idx2 = idx + stride;
+            const double v0 = b.src[off(idx, b.ss)];
+            double v1 = 0.0;
+            if (idx2 < total) v1 = b.src[off(idx2, b.ss)];
+            b.dst[off(idx, b.ds)] = v0;
+            if (idx2 < total) b.dst[off(idx2, b.ds)] = v1;
         }
     }
-    if (use_flags) {
+    if (mode == 1 || mode == 2) {
         __syncthreads();
         if (threadIdx.x == 0) {
-            __threadfence();
+            __threadfence_system();  // this block's (peer) stores are visible before the flag
             const unsigned int nblocks = gridDim.x * gridDim.y;
             if (atomicAdd(arrive, 1u) == nblocks - 1) {
                 *arrive = 0;  // ready for the next launch (stream order)
-                for (int p = 0; p < sync.npeers; ++p) post_flag(sync.post_done[p], step);
+                __threadfence_system();
+                for (int p = 0; p < sync.npeers; ++p)
+                    post_flag(mode == 1 ? sync.post_done[p] : sync.post_ready[p], step);
             }
         }
     }
@@ -149,6 +175,7 @@ int b200_halo_refresh(const b200_halo_box *boxes_dev, int nboxes, int blocks_per
 {
     using namespace b200;
     B200_REQUIRE(nboxes >= 0 && blocks_per_box > 0, "halo_refresh: bad launch shape");
+    B200_REQUIRE(use_flags >= 0 && use_flags <= 3, "halo_refresh: unknown mode %d", use_flags);
     if (nboxes == 0 && !use_flags) return B200_OK;
     B200_REQUIRE(nboxes == 0 || boxes_dev, "halo_refresh: boxes is null");
     HaloSync s;

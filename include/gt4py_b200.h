@@ -160,8 +160,11 @@ typedef struct b200_halo_sync {
 B200_API int b200_ipc_get_mem_handle(void *dptr, unsigned char handle[64]);
 B200_API int b200_ipc_open_mem_handle(const unsigned char handle[64], void **dptr);
 B200_API int b200_ipc_close_mem_handle(void *dptr);
-/* boxes_dev: device array of nboxes boxes.  use_flags = 0 skips the inter-rank protocol (single-process
- * tests, or when the caller orders ranks itself).  arrive_dev: zero-initialised device counter. */
+/* boxes_dev: device array of nboxes boxes; arrive_dev: zero-initialised device counter.  `use_flags` is the
+ * protocol mode: 0 = plain box copy (single-process tests, or the caller orders the ranks itself);
+ * 1 = PULL (post ready, wait ready, copy from peer memory, post done); 2 = PUSH (copy into the neighbours'
+ * staging buffers, then post ready); 3 = UNPACK (wait ready, copy local staging -> halo).  The fast path is
+ * one PUSH launch followed by one UNPACK launch per refresh. */
 B200_API int b200_halo_refresh(const b200_halo_box *boxes_dev, int nboxes, int blocks_per_box,
                       const b200_halo_sync *sync, uint64_t step, unsigned int *arrive_dev,
                       int use_flags, void *stream);

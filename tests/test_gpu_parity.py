@@ -171,8 +171,9 @@ def test_full_size_properties_vadv():
     assert np.array_equal(out[ni], f["utens_stage"][ni])  # the i+1 halo column is not written
 
 
+@pytest.mark.parametrize("mode", ["push", "pull"])
 @pytest.mark.parametrize("world", [2, 4])
-def test_halo_refresh_single_device_emulation(world):
+def test_halo_refresh_single_device_emulation(world, mode):
     """All ranks of a Px x Py decomposition emulated in this process on one device (no flags, host
     ordering): the pull kernel must restore stale halos so that the decomposed hdiff / vadv equal the
     single-domain oracle bit-for-bit."""
@@ -206,14 +207,14 @@ def test_halo_refresh_single_device_emulation(world):
         fields = {"in_field": _dev(loc, (2, 2, 0)), "out_field": _dev(np.zeros_like(loc), (2, 2, 0)),
                   "coeff": _dev(np.full_like(loc, 0.025), (2, 2, 0))}
         fields.update({k: _dev(v, (0, 0, 0)) for k, v in L.items()})
-        ex = HaloExchanger(None, d, use_flags=False)
+        ex = HaloExchanger(None, d, use_flags=False, mode=mode)
         ex.add_group([(fields["in_field"], (2, 2, 0), dom, ((2, 2), (2, 2))),
                       (fields["wcon"], (0, 0, 0), dom, ((0, 1), (0, 0)))])
         exs.append(ex)
         dev.append(fields)
     HaloExchanger.finalize_local(exs)
-    for ex in exs:
-        ex.refresh(0)
+    HaloExchanger.refresh_local(exs, 0)
+    HaloExchanger.refresh_local(exs, 0)  # second refresh uses the other staging parity
     gb.synchronize()
     for d, f in zip(decs, dev):
         x, y = d.coords

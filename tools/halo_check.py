@@ -53,7 +53,7 @@ def main():
          "out_field": storage.zeros(loc.shape, aligned_index=(2, 2, 0)),
          "coeff": storage.from_array(np.full_like(loc, 0.025), aligned_index=(2, 2, 0))}
     f.update({k: storage.from_array(v) for k, v in L.items()})
-    ex = HaloExchanger(TorchComm(dist), d)
+    ex = HaloExchanger(TorchComm(dist), d, mode=os.environ.get("HALO_MODE", "push"))
     ex.add_group([(f["in_field"], (2, 2, 0), dom, ((2, 2), (2, 2))), (f["wcon"], (0, 0, 0), dom, ((0, 1), (0, 0)))])
     ex.finalize()
     ex.refresh(0)
