@@ -77,7 +77,7 @@ class Field(Structure):
 
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_PKG, "lib", "libgt4py_b200.so")
+LIB_PATH = os.environ.get("GT4PY_B200_LIB") or os.path.join(_PKG, "lib", "libgt4py_b200.so")
 _lib = None
 
 _VP = c_void_p

@@ -158,6 +158,118 @@ hdiff_jmarch(View3<const double> in, View3<double> out, View3<const double> coef
     }
 }
 
+// One J-strip of one K-plane.  REV = false marches towards +J, REV = true towards -J: the marching row r of a
+// reversed strip is the real row (j0 + jend - 1 - r).  Neighbouring strips march in OPPOSITE directions, so
+// the 4 rows two strips share are read by both at the same time (both at the start or both at the end of
+// their march) and the second read is an L2 hit; with a common direction the reads are a whole march
+// (~30 us) apart and the line has long been evicted by the streaming traffic (ncu: +12.5 % in_field bytes).
+// The reversed strip evaluates the same expression tree: under j -> -j the limited fluxes change sign
+// exactly (the limiter test res * d is invariant), x + (-a) == x - a and x - (-b) == x + b in IEEE
+// arithmetic, so ((X + fly[j]) - fly[j-1]) is computed as ((X - prev) + cur).
+template <bool LIMITER, int PF, bool REV>
+__device__ __forceinline__ void hdiff_strip(const View3<const double> &in, const View3<double> &out,
+                                            const View3<const double> &coeff, int ni, int nj, int tj)
+{
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const int wpb = blockDim.x >> 5;
+    const int col = (blockIdx.x * wpb + warp) * JM_COLS_PER_WARP - 2 + 2 * lane;
+    const int j0 = blockIdx.y * tj;
+    const int k = blockIdx.z;
+    if (col - 2 * lane + 2 >= ni) return;  // first produced column >= ni: whole warp idle (uniform)
+    const int jend = min(j0 + tj, nj);  // exclusive end of output rows
+    const int mirror = j0 + jend - 1;   // REV: real row = mirror - marching row
+
+    const double *__restrict__ pin = in.p + (int64_t)k * in.sk;
+    const double *__restrict__ pco = coeff.p + (int64_t)k * coeff.sk;
+    double *__restrict__ pout = out.p + (int64_t)k * out.sk;
+    const int64_t sj = in.sj;
+
+    const bool store_x = lane >= 1 && lane <= 30 && col < ni;
+    const bool store_y = lane >= 1 && lane <= 30 && col + 1 < ni;
+
+    auto load_in = [&](int r) -> double2 {
+        // forward: r >= j0 - 2 >= -2 always; reverse: real <= jend + 1 <= nj + 1 always -> one compare each
+        const int real = REV ? mirror - r : r;
+        const bool ok = REV ? real >= -2 : real < nj + 2;
+        return ok ? load_pair(pin + (int64_t)real * sj, col, ni) : make_double2(0.0, 0.0);
+    };
+    auto load_co = [&](int r) -> double2 {
+        double2 v = make_double2(0.0, 0.0);
+        if (r >= j0 && r < jend) {
+            const double *row = pco + (int64_t)(REV ? mirror - r : r) * coeff.sj;
+            if (store_y) v = __ldcs(reinterpret_cast<const double2 *>(row + col));
+            else if (store_x) v.x = __ldcs(row + col);
+        }
+        return v;
+    };
+
+    // rolling window (marching rows)
+    double2 in0 = load_in(j0 - 2);
+    double2 in1 = load_in(j0 - 1);
+    double2 nin[PF], nco[PF];  // prefetch queues: rows jr+2 .. jr+1+PF of in, rows jr .. of coeff
+#pragma unroll
+    for (int u = 0; u < PF; ++u) {
+        nin[u] = load_in(j0 + u);
+        nco[u] = load_co(j0 - 2 + u);
+    }
+    double2 lap0 = make_double2(0.0, 0.0), flym1 = make_double2(0.0, 0.0);
+    double r0 = 0.0, lapr0 = 0.0;  // in(b+1, row jr) and lap(b+1, row jr)
+
+    for (int jb = j0 - 2; jb < jend; jb += PF) {
+#pragma unroll
+        for (int u = 0; u < PF; ++u) {
+            const int jr = jb + u;  // the marching row whose output is produced in this step
+            double2 in2 = nin[u];
+            double2 co = nco[u];
+            nin[u] = load_in(jr + 2 + PF);
+            nco[u] = load_co(jr + PF);
+            // Laplacian of row jr+1 on the own two columns:  4*in - (((in[+1,0] + in[-1,0]) + in[0,+1]) + in[0,-1])
+            double l1 = __shfl_up_sync(0xffffffffu, in1.y, 1);    // in(a-1, jr+1)
+            double r1 = __shfl_down_sync(0xffffffffu, in1.x, 1);  // in(b+1, jr+1)
+            const double2 jp = REV ? in0 : in2;  // real row +1
+            const double2 jm = REV ? in2 : in0;  // real row -1
+            double2 lap1;
+            lap1.x = 4.0 * in1.x - (((in1.y + l1) + jp.x) + jm.x);
+            lap1.y = 4.0 * in1.y - (((r1 + in1.x) + jp.y) + jm.y);
+            double lapr1 = __shfl_down_sync(0xffffffffu, lap1.x, 1);  // lap(b+1, jr+1)
+            // fluxes of row jr
+            double2 fly;
+            fly.x = limit<LIMITER>(lap1.x - lap0.x, in1.x - in0.x);
+            fly.y = limit<LIMITER>(lap1.y - lap0.y, in1.y - in0.y);
+            double fa = limit<LIMITER>(lap0.y - lap0.x, in0.y - in0.x);  // flx(a, jr)
+            double fb = limit<LIMITER>(lapr0 - lap0.y, r0 - in0.y);      // flx(b, jr)
+            double fl = __shfl_up_sync(0xffffffffu, fb, 1);              // flx(a-1, jr)
+            if (jr >= j0 && jr < jend) {
+                double2 o;
+                if (REV) {  // fly == -fly_real[j-1], flym1 == -fly_real[j]
+                    o.x = in0.x - co.x * (((fa - fl) - flym1.x) + fly.x);
+                    o.y = in0.y - co.y * (((fb - fa) - flym1.y) + fly.y);
+                } else {
+                    o.x = in0.x - co.x * (((fa - fl) + fly.x) - flym1.x);
+                    o.y = in0.y - co.y * (((fb - fa) + fly.y) - flym1.y);
+                }
+                double *row = pout + (int64_t)(REV ? mirror - jr : jr) * out.sj;
+                if (store_y) __stcs(reinterpret_cast<double2 *>(row + col), o);
+                else if (store_x) __stcs(row + col, o.x);
+            }
+            // roll
+            in0 = in1; in1 = in2; lap0 = lap1; flym1 = fly; r0 = r1; lapr0 = lapr1;
+        }
+    }
+}
+
+template <bool LIMITER, int PF, int MINB>
+__global__ void __launch_bounds__(256, MINB)
+hdiff_jmarch_alt(View3<const double> in, View3<double> out, View3<const double> coeff, int ni, int nj,
+                 int nk, int tj)
+{
+    if (blockIdx.y & 1)
+        hdiff_strip<LIMITER, PF, true>(in, out, coeff, ni, nj, tj);
+    else
+        hdiff_strip<LIMITER, PF, false>(in, out, coeff, ni, nj, tj);
+}
+
 // ------------------------------------------------------------------------------------------------
 // host dispatch
 // ------------------------------------------------------------------------------------------------
@@ -175,7 +287,7 @@ static int launch_hdiff(View3<const double> in, View3<double> out, View3<const d
         dim3 block(64, 4, 1);
         dim3 grid((ni + 63) / 64, (nj + 3) / 4, nk);
         hdiff_point<LIMITER><<<grid, block, 0, stream>>>(in, out, co, ni, nj, nk);
-    } else if (variant == 2 || variant == 3) {
+    } else if (variant >= 2 && variant <= 4) {
         if (!fast_ok) {
             set_error("hdiff variant %d needs unit I stride, 16-byte aligned origins and even J/K strides", variant);
             return B200_EUNSUP;
@@ -195,8 +307,10 @@ static int launch_hdiff(View3<const double> in, View3<double> out, View3<const d
         dim3 grid((nwarps + wpb - 1) / wpb, (nj + tj - 1) / tj, nk);
         if (variant == 2)
             hdiff_jmarch<LIMITER, 2><<<grid, block, 0, stream>>>(in, out, co, ni, nj, nk, tj);
-        else
+        else if (variant == 3)
             hdiff_jmarch<LIMITER, 4><<<grid, block, 0, stream>>>(in, out, co, ni, nj, nk, tj);
+        else  // variant 4: alternating march directions (less DRAM traffic, not faster: see DESIGN.md 3.1)
+            hdiff_jmarch_alt<LIMITER, 2, 4><<<grid, block, 0, stream>>>(in, out, co, ni, nj, nk, tj);
     } else {
         set_error("hdiff: unknown variant %d", variant);
         return B200_EUNSUP;
