@@ -96,6 +96,8 @@ _PROTOTYPES = {
     "b200_memcpy_h2d": ([_VP, _VP, c_size_t, _VP], c_int),
     "b200_memcpy_d2h": ([_VP, _VP, c_size_t, _VP], c_int),
     "b200_memcpy_d2d": ([_VP, _VP, c_size_t, _VP], c_int),
+    "b200_memcpy2d_h2d": ([_VP, c_size_t, _VP, c_size_t, c_size_t, c_size_t, _VP], c_int),
+    "b200_memcpy2d_d2h": ([_VP, c_size_t, _VP, c_size_t, c_size_t, c_size_t, _VP], c_int),
     "b200_memset": ([_VP, c_int, c_size_t, _VP], c_int),
     "b200_stream_create": ([POINTER(_VP)], c_int),
     "b200_stream_destroy": ([_VP], c_int),

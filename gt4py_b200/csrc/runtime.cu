@@ -94,6 +94,24 @@ static int copy(void *dst, const void *src, size_t bytes, void *stream, cudaMemc
 int b200_memcpy_h2d(void *d, const void *s, size_t n, void *st) { return copy(d, s, n, st, cudaMemcpyHostToDevice); }
 int b200_memcpy_d2h(void *d, const void *s, size_t n, void *st) { return copy(d, s, n, st, cudaMemcpyDeviceToHost); }
 int b200_memcpy_d2d(void *d, const void *s, size_t n, void *st) { return copy(d, s, n, st, cudaMemcpyDeviceToDevice); }
+static int copy2d(void *dst, size_t dpitch, const void *src, size_t spitch, size_t width, size_t height,
+                  void *stream, cudaMemcpyKind kind)
+{
+    if (width == 0 || height == 0) return B200_OK;
+    B200_REQUIRE(dst && src, "memcpy2d: null pointer");
+    B200_REQUIRE(width <= dpitch && width <= spitch, "memcpy2d: width larger than pitch");
+    B200_CUDA_CHECK(cudaMemcpy2DAsync(dst, dpitch, src, spitch, width, height, kind, (cudaStream_t)stream));
+    if (!stream) B200_CUDA_CHECK(cudaStreamSynchronize(0));
+    return B200_OK;
+}
+int b200_memcpy2d_h2d(void *d, size_t dp, const void *s, size_t sp, size_t w, size_t h, void *st)
+{
+    return copy2d(d, dp, s, sp, w, h, st, cudaMemcpyHostToDevice);
+}
+int b200_memcpy2d_d2h(void *d, size_t dp, const void *s, size_t sp, size_t w, size_t h, void *st)
+{
+    return copy2d(d, dp, s, sp, w, h, st, cudaMemcpyDeviceToHost);
+}
 int b200_memset(void *dst, int value, size_t bytes, void *stream)
 {
     if (bytes == 0) return B200_OK;

@@ -89,6 +89,11 @@ B200_API int b200_host_free(void *hptr);
 B200_API int b200_memcpy_h2d(void *dst, const void *src, size_t bytes, void *stream);
 B200_API int b200_memcpy_d2h(void *dst, const void *src, size_t bytes, void *stream);
 B200_API int b200_memcpy_d2d(void *dst, const void *src, size_t bytes, void *stream);
+/* pitched copies (height rows of `width` bytes): a J-slab of an I-contiguous field is one of these */
+B200_API int b200_memcpy2d_h2d(void *dst, size_t dpitch, const void *src, size_t spitch, size_t width,
+                      size_t height, void *stream);
+B200_API int b200_memcpy2d_d2h(void *dst, size_t dpitch, const void *src, size_t spitch, size_t width,
+                      size_t height, void *stream);
 B200_API int b200_memset(void *dst, int value, size_t bytes, void *stream);
 
 /* ---- streams / events ------------------------------------------------------------------- */
