@@ -1,0 +1,216 @@
+"""Run-time half of the OIR lowering: load a *plan* (+ CUDA source) produced by ``gt4py_b200.lowering`` and
+expose it as a stencil object.  Does not import gt4py -- this is what runs on the GPU box.
+
+    st = generated.load_plan("tests/golden/generated/horizontal_regions")   # dir with plan.json + kernel.cu
+    st(in_f, out_f, origin=(1, 1, 0), domain=(ni, nj, nk))
+
+The kernels are compiled once with ``nvcc -cubin`` for sm_100a (cached next to the source), loaded through
+``b200_module_load`` and launched with ``b200_launch`` (include/gt4py_b200.h); fields cross as raw pointers
+and element strides packed into the generated ``struct Args``.  There is no CPU fallback: without nvcc or
+without a device, loading / calling raises.
+"""
+from __future__ import annotations
+
+import ctypes
+import hashlib
+import json
+import os
+import subprocess
+from ctypes import byref, c_void_p
+from typing import Any, Dict
+
+import numpy as np
+
+from . import _lib, build as _build, storage
+from .stencil_object import AccessKind, Boundary, DomainInfo, FieldInfo, ParameterInfo, StencilObject
+
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo", "-fmad=false",
+              "-prec-div=true", "-prec-sqrt=true"]
+_CT = {"bool": ctypes.c_bool, "int8": ctypes.c_int8, "int16": ctypes.c_int16, "int32": ctypes.c_int32,
+       "int64": ctypes.c_int64, "float32": ctypes.c_float, "float64": ctypes.c_double}
+
+
+def compile_cubin(src_path: str) -> str:
+    """nvcc -cubin, cached by source hash next to the source."""
+    with open(src_path, "rb") as fh:
+        digest = hashlib.sha256(fh.read() + " ".join(NVCC_FLAGS).encode()).hexdigest()[:16]
+    out = os.path.splitext(src_path)[0] + f".{digest}.cubin"
+    if not os.path.exists(out):
+        cmd = [_build.nvcc(), *NVCC_FLAGS, "-cubin", "-o", out, src_path]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode:
+            raise RuntimeError(f"nvcc failed on generated source {src_path}:\n{r.stderr}")
+    return out
+
+
+class _Module:
+    """A loaded cubin and its kernels."""
+
+    def __init__(self, cubin_path: str, names):
+        with open(cubin_path, "rb") as fh:
+            self.image = fh.read()
+        self.handle = c_void_p()
+        buf = ctypes.create_string_buffer(self.image, len(self.image))
+        _lib.check(_lib.lib().b200_module_load(buf, len(self.image), byref(self.handle)))
+        self.kernels = {}
+        for n in names:
+            k = c_void_p()
+            _lib.check(_lib.lib().b200_module_get_kernel(self.handle, n.encode(), byref(k)))
+            self.kernels[n] = k
+
+
+def _args_struct(plan):
+    fields = []
+    for name, kind, dtype, nstr in plan["args"]:
+        if kind == "field":
+            fields.append((name, c_void_p))
+            fields.append((name + "_s", ctypes.c_int64 * nstr))
+        else:
+            fields.append((name, _CT[dtype]))
+    fields += [("ni", ctypes.c_int32), ("nj", ctypes.c_int32), ("nk", ctypes.c_int32)]
+    return type("Args", (ctypes.Structure,), {"_fields_": fields})
+
+
+class GeneratedStencil(StencilObject):
+    """Base of plan-driven stencils; subclasses are created by `load_plan`."""
+
+    _plan_: Dict[str, Any] = {}
+    _dir_: str = ""
+    _use_library_ = True  # False: always run the lowered kernels (tests compare the two paths)
+
+    @classmethod
+    def _module(cls):
+        if cls.__dict__.get("_mod") is None:
+            cubin = compile_cubin(os.path.join(cls._dir_, cls._plan_.get("source", "kernel.cu")))
+            cls._mod = _Module(cubin, [k["name"] for k in cls._plan_["kernels"]])
+            for k in cls._plan_["kernels"]:
+                if k.get("smem_bytes", 0) > 48 * 1024:  # opt in to more than the default dynamic shared memory
+                    _lib.check(_lib.lib().b200_kernel_set_smem(cls._mod.kernels[k["name"]], int(k["smem_bytes"])))
+            cls._Args = _args_struct(cls._plan_)
+            cls._scratch = {}
+        return cls._mod
+
+    def _temporaries(self, domain):
+        """Global scratch for the OIR temporaries, cached per domain (owned by the stencil class)."""
+        cls = type(self)
+        hit = cls._scratch.get(domain)
+        if hit is None:
+            hit = {}
+            ni, nj, nk = domain
+            for t in cls._plan_["temporaries"]:
+                (li, hi), (lj, hj) = t["pad"]
+                shape = [ni + li + hi if t["dims"][0] else 1, nj + lj + hj if t["dims"][1] else 1,
+                         nk if t["dims"][2] else 1] + list(t["data_dims"])
+                arr = storage.zeros(shape, np.dtype(t["dtype"]), aligned_index=(li, lj, 0) + (0,) * len(t["data_dims"]),
+                                    dimensions=["I", "J", "K"] + [str(d) for d in range(len(t["data_dims"]))])
+                item = arr.dtype.itemsize
+                strides = [s // item for s in arr.strides]
+                for d in range(3):
+                    if not t["dims"][d]:
+                        strides[d] = 0
+                origin_ptr = arr.ptr + (li * arr.strides[0] if t["dims"][0] else 0) + (lj * arr.strides[1] if t["dims"][1] else 0)
+                hit[t["name"]] = (arr, origin_ptr, strides)
+            cls._scratch = {domain: hit}  # keep one domain's worth
+        return hit
+
+    def _launch_library(self, lib_plan, domain, fields, params, stream):
+        """The stencil was recognised as one the library has a hand-written kernel for (backend.library_match)."""
+        L, arg, sh = _lib.lib(), lib_plan["args"], _lib.stream_handle(stream)
+        dom = (ctypes.c_int64 * 3)(*domain)
+        f = {role: byref(fields[name]) for role, name in arg.items() if name in fields}
+        variant = int(os.environ.get("B200_LIBRARY_VARIANT", "0"))
+        if lib_plan["kernel"] == "hdiff":
+            rc = L.b200_hdiff(f["in_field"], f["out_field"], f["coeff"], dom, int(lib_plan["limiter"]), variant, sh)
+        elif lib_plan["kernel"] == "vadv":
+            rc = L.b200_vadv(f["utens_stage"], f["u_stage"], f["wcon"], f["u_pos"], f["utens"],
+                             ctypes.c_double(params[arg["dtr_stage"]]), dom, variant, sh)
+        elif lib_plan["kernel"] == "tridiag":
+            rc = L.b200_tridiag(f["inf"], f["diag"], f["sup"], f["rhs"], f["out"], dom, variant, sh)
+        else:
+            raise RuntimeError(f"plan names an unknown library kernel {lib_plan['kernel']!r}")
+        _lib.check(rc)
+
+    def _launch(self, domain, fields, params, stream):
+        cls = type(self)
+        lib_plan = cls._plan_.get("library")
+        if lib_plan is not None and cls._use_library_ and domain[2] >= lib_plan.get("min_k", 1):
+            return self._launch_library(lib_plan, domain, fields, params, stream)
+        mod = cls._module()
+        a = cls._Args()
+        a.ni, a.nj, a.nk = domain
+        for spec in cls._plan_["fields"]:
+            name = spec["name"]
+            f = fields.get(name)
+            if f is None:  # unreferenced / optional field passed as None
+                setattr(a, name, None)
+                continue
+            item = np.dtype(spec["dtype"]).itemsize
+            # the descriptor's axes are the field's own (masked) axes; the kernel indexes I, J, K, data...
+            strides, ptr, pos = [0, 0, 0], f.ptr, 0
+            for d in range(3):
+                if spec["dims"][d]:
+                    strides[d] = f.stride[pos]
+                    ptr += f.origin[pos] * f.stride[pos] * item
+                    pos += 1
+            strides += [f.stride[pos + n] for n in range(len(spec["data_dims"]))]
+            setattr(a, name, ptr)
+            getattr(a, name + "_s")[:] = strides
+        for name, (arr, origin_ptr, strides) in self._temporaries(tuple(domain)).items():
+            setattr(a, name, origin_ptr)
+            getattr(a, name + "_s")[:] = strides
+        for s in cls._plan_["scalars"]:
+            setattr(a, s["name"], params[s["name"]])
+        ni, nj, nk = domain
+        argp = (c_void_p * 1)(ctypes.cast(byref(a), c_void_p))
+        sh = _lib.stream_handle(stream)
+        for k in cls._plan_["kernels"]:
+            wi = ni + k["i_ext"][1] - k["i_ext"][0]
+            wj = nj + k["j_ext"][1] - k["j_ext"][0]
+            if wi <= 0 or wj <= 0:
+                continue
+            smem = 0
+            if k["kind"] == "point":
+                block, grid = (64, 4, 1), ((wi + 63) // 64, (wj + 3) // 4, nk)
+            elif k["kind"] == "tile":  # a CTA per TI x TJ tile of the compute domain and level; halo recomputed
+                ti, tj = k["tile"]
+                block, grid, smem = (256, 1, 1), ((ni + ti - 1) // ti, (nj + tj - 1) // tj, nk), k["smem_bytes"]
+            else:
+                block, grid = (32, 4, 1), ((wi + 31) // 32, (wj + 3) // 4, 1)
+            if nk <= 0 and k["kind"] != "column":
+                continue
+            _lib.check(_lib.lib().b200_launch(mod.kernels[k["name"]], (ctypes.c_uint32 * 3)(*grid),
+                                              (ctypes.c_uint32 * 3)(*block), smem, sh, argp, 1))
+
+
+def stencil_class(plan: Dict[str, Any], directory: str):
+    """Build the stencil class described by `plan` (plan["info"] holds the reference's args data)."""
+    info = plan["info"]
+    finfo = {}
+    for name, fi in info["field_info"].items():
+        if fi is None:
+            finfo[name] = FieldInfo(AccessKind.NONE, Boundary(((0, 0), (0, 0), (0, 0))), ("I", "J", "K"), (), np.dtype("float64"))
+            continue
+        finfo[name] = FieldInfo(AccessKind(fi["access"]), Boundary(fi["boundary"]), tuple(fi["axes"]),
+                                tuple(fi["data_dims"]), np.dtype(fi["dtype"]))
+    pinfo = {name: (ParameterInfo(AccessKind(pi["access"]), np.dtype(pi["dtype"])) if pi is not None
+                    else ParameterInfo(AccessKind.NONE, np.dtype("float64")))
+             for name, pi in info["parameter_info"].items()}
+    di = info["domain_info"]
+    attrs = {
+        "_plan_": plan, "_dir_": directory, "_arg_names_": tuple(info["arg_names"]),
+        "_arg_defaults_": dict(info.get("arg_defaults", {})),
+        "_gt_domain_info_": DomainInfo(tuple(di["parallel_axes"]), di["sequential_axis"],
+                                       di["min_sequential_axis_size"], di["ndim"]),
+        "_gt_field_info_": finfo, "_gt_parameter_info_": pinfo,
+        "_gt_options_": {"name": plan["name"], "module": __name__},
+    }
+    return type(f"{plan['name']}__b200", (GeneratedStencil,), attrs)
+
+
+def load_plan(directory: str, use_library: bool = True):
+    """Stencil object for the plan in `directory` (plan.json + the CUDA source it names)."""
+    with open(os.path.join(directory, "plan.json")) as fh:
+        plan = json.load(fh)
+    cls = stencil_class(plan, directory)
+    cls._use_library_ = bool(use_library)
+    return cls()
