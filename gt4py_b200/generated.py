@@ -82,10 +82,12 @@ class GeneratedStencil(StencilObject):
     def _module(cls):
         if cls.__dict__.get("_mod") is None:
             cubin = compile_cubin(os.path.join(cls._dir_, cls._plan_.get("source", "kernel.cu")))
-            cls._mod = _Module(cubin, [k["name"] for k in cls._plan_["kernels"]])
+            names = [k["name"] + sfx for k in cls._plan_["kernels"] for sfx in ("", "_u")]
+            cls._mod = _Module(cubin, names)
             for k in cls._plan_["kernels"]:
                 if k.get("smem_bytes", 0) > 48 * 1024:  # opt in to more than the default dynamic shared memory
-                    _lib.check(_lib.lib().b200_kernel_set_smem(cls._mod.kernels[k["name"]], int(k["smem_bytes"])))
+                    for sfx in ("", "_u"):
+                        _lib.check(_lib.lib().b200_kernel_set_smem(cls._mod.kernels[k["name"] + sfx], int(k["smem_bytes"])))
             cls._Args = _args_struct(cls._plan_)
             cls._scratch = {}
         return cls._mod
@@ -138,6 +140,7 @@ class GeneratedStencil(StencilObject):
         mod = cls._module()
         a = cls._Args()
         a.ni, a.nj, a.nk = domain
+        unit = True  # every field I-contiguous -> the <kernel>_u entry points (stride folded to 1)
         for spec in cls._plan_["fields"]:
             name = spec["name"]
             f = fields.get(name)
@@ -153,11 +156,14 @@ class GeneratedStencil(StencilObject):
                     ptr += f.origin[pos] * f.stride[pos] * item
                     pos += 1
             strides += [f.stride[pos + n] for n in range(len(spec["data_dims"]))]
+            span = sum((int(f.shape[n]) - 1) * abs(int(f.stride[n])) for n in range(int(f.ndim)))
+            unit = unit and (not spec["dims"][0] or strides[0] == 1) and span < (1 << 31) - (1 << 20)
             setattr(a, name, ptr)
             getattr(a, name + "_s")[:] = strides
         for name, (arr, origin_ptr, strides) in self._temporaries(tuple(domain)).items():
             setattr(a, name, origin_ptr)
             getattr(a, name + "_s")[:] = strides
+            unit = unit and (strides[0] in (0, 1))
         for s in cls._plan_["scalars"]:
             setattr(a, s["name"], params[s["name"]])
         ni, nj, nk = domain
@@ -173,12 +179,12 @@ class GeneratedStencil(StencilObject):
                 block, grid = (64, 4, 1), ((wi + 63) // 64, (wj + 3) // 4, nk)
             elif k["kind"] == "tile":  # a CTA per TI x TJ tile of the compute domain and level; halo recomputed
                 ti, tj = k["tile"]
-                block, grid, smem = (256, 1, 1), ((ni + ti - 1) // ti, (nj + tj - 1) // tj, nk), k["smem_bytes"]
+                block, grid, smem = (*k["block"], 1), ((ni + ti - 1) // ti, (nj + tj - 1) // tj, nk), k["smem_bytes"]
             else:
                 block, grid = (32, 4, 1), ((wi + 31) // 32, (wj + 3) // 4, 1)
             if nk <= 0 and k["kind"] != "column":
                 continue
-            _lib.check(_lib.lib().b200_launch(mod.kernels[k["name"]], (ctypes.c_uint32 * 3)(*grid),
+            _lib.check(_lib.lib().b200_launch(mod.kernels[k["name"] + ("_u" if unit else "")], (ctypes.c_uint32 * 3)(*grid),
                                               (ctypes.c_uint32 * 3)(*block), smem, sh, argp, 1))
 
 

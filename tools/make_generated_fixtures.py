@@ -74,6 +74,12 @@ def definitions():
     defs["exec_info_diffusion"] = (tei.TestExecInfo.diffusion_def, {})
     for name, (fn, ext) in chain.DEFINITIONS.items():
         defs[name] = (fn, ext)
+    # the same stencils forced through the other lowering than the backend's own choice, to cover both
+    for name in ("horizontal_diffusion", "simple_horizontal_diffusion", "exec_info_advection", "native_functions",
+                 "horizontal_region_with_conditional", "form_land_mask", "data_types"):
+        defs[name + "__tile"] = (*defs[name][:2], {"fuse_temporaries": True})
+    for name in ("fv3_chain", "exec_info_diffusion"):
+        defs[name + "__point"] = (*defs[name][:2], {"fuse_temporaries": False})
     return defs
 
 
@@ -86,10 +92,11 @@ def main():
     names = sys.argv[1:] or sorted(defs)
     report = {}
     for name in names:
-        fn, ext = defs[name]
+        fn, ext, *opts = defs[name]
+        opts = opts[0] if opts else {}
         try:
             ref = gtscript.stencil("numpy", fn, externals=ext, format_source=False, rebuild=True, name=name)
-            b2 = gtscript.stencil("b200", fn, externals=ext, format_source=False, rebuild=True, name=name)
+            b2 = gtscript.stencil("b200", fn, externals=ext, format_source=False, rebuild=True, name=name, **opts)
         except Exception as exc:  # unsupported feature: recorded, not hidden
             report[name] = f"{type(exc).__name__}: {str(exc)[:200]}"
             print("SKIP", name, report[name])
