@@ -360,10 +360,8 @@ class HaloExchanger:
     @classmethod
     def for_bench(cls, dist, rank, world, local, hsets, vsets, dom, mode="p2p"):
         ex = cls(TorchComm(dist), Decomposition.create(world, rank), mode=mode)
-        for h, v in zip(hsets, vsets):
-            ex.add_group([
-                (h["in_field"], (2, 2, 0), dom, ((2, 2), (2, 2))),   # field_info['in_field'].boundary
-                (v["wcon"], (0, 0, 0), dom, ((0, 1), (0, 0))),       # field_info['wcon'].boundary
-            ])
+        for h, v in zip(hsets, vsets):  # field set s -> groups 2s (in_field) and 2s + 1 (wcon)
+            ex.add_group([(h["in_field"], (2, 2, 0), dom, ((2, 2), (2, 2)))])   # field_info['in_field'].boundary
+            ex.add_group([(v["wcon"], (0, 0, 0), dom, ((0, 1), (0, 0)))])       # field_info['wcon'].boundary
         ex.finalize()
         return ex
