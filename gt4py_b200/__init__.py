@@ -13,7 +13,7 @@ There is no CPU or PyTorch fallback anywhere in this package.
 """
 from . import _lib, storage, stencil_object  # noqa: F401
 from ._lib import B200Error, Event, Stream, device_count, synchronize  # noqa: F401
-from .stencil_object import FrozenStencil, StencilObject, use_stream  # noqa: F401
+from .stencil_object import FrozenStencil, Graph, StencilObject, use_stream  # noqa: F401
 from .hostio import HostPipeline  # noqa: F401,E402
 
 __version__ = "0.1.0"

@@ -107,6 +107,10 @@ _PROTOTYPES = {
     "b200_event_record": ([_VP, _VP], c_int),
     "b200_event_sync": ([_VP], c_int),
     "b200_event_elapsed_ms": ([_VP, _VP, POINTER(c_float)], c_int),
+    "b200_graph_begin": ([_VP], c_int),
+    "b200_graph_end": ([_VP, POINTER(_VP)], c_int),
+    "b200_graph_launch": ([_VP, _VP], c_int),
+    "b200_graph_destroy": ([_VP], c_int),
     "b200_stream_wait_event": ([_VP, _VP], c_int),
     "b200_hdiff": ([POINTER(Field), POINTER(Field), POINTER(Field), POINTER(c_int64), c_int, c_int, _VP], c_int),
     "b200_vadv": ([POINTER(Field)] * 5 + [c_double, POINTER(c_int64), c_int, _VP], c_int),

@@ -169,6 +169,37 @@ int b200_stream_wait_event(void *stream, void *event)
     return B200_OK;
 }
 
+// ---- CUDA graphs ----------------------------------------------------------------------------
+int b200_graph_begin(void *stream)
+{
+    B200_REQUIRE(stream, "graph_begin: capture needs an explicit (non-default) stream");
+    B200_CUDA_CHECK(cudaStreamBeginCapture((cudaStream_t)stream, cudaStreamCaptureModeRelaxed));
+    return B200_OK;
+}
+int b200_graph_end(void *stream, void **graph_exec)
+{
+    B200_REQUIRE(stream && graph_exec, "graph_end: bad arguments");
+    cudaGraph_t graph = nullptr;
+    B200_CUDA_CHECK(cudaStreamEndCapture((cudaStream_t)stream, &graph));
+    cudaGraphExec_t exec = nullptr;
+    cudaError_t err = cudaGraphInstantiate(&exec, graph, 0);
+    cudaGraphDestroy(graph);
+    B200_CUDA_CHECK(err);
+    *graph_exec = exec;
+    return B200_OK;
+}
+int b200_graph_launch(void *graph_exec, void *stream)
+{
+    B200_REQUIRE(graph_exec, "graph_launch: null graph");
+    B200_CUDA_CHECK(cudaGraphLaunch((cudaGraphExec_t)graph_exec, (cudaStream_t)stream));
+    return B200_OK;
+}
+int b200_graph_destroy(void *graph_exec)
+{
+    if (graph_exec) B200_CUDA_CHECK(cudaGraphExecDestroy((cudaGraphExec_t)graph_exec));
+    return B200_OK;
+}
+
 // ---- generated-stencil modules: cubin images built by the Python backend with nvcc ----------
 int b200_module_load(const void *image, size_t bytes, void **module)
 {

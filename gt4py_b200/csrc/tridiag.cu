@@ -73,6 +73,86 @@ __global__ void __launch_bounds__(128) tridiag_column(TriArgs a)
     }
 }
 
+// Variants 2..: the same column walk with (a) a register budget that lets more columns be resident per SM
+// (the kernel is bound by load latency: ncu of variant 1 shows 19 of 64 warps active at 84 registers, 51 % of DRAM
+// throughput, long-scoreboard stalls), (b) a prefetch queue in the BACKWARD sweep too, whose loads of the parked
+// (sup, rhs) otherwise each wait out an L2 / DRAM round trip.
+template <int PF, int BPF, int MINB>
+__global__ void __launch_bounds__(128, MINB) tridiag_column_q(TriArgs a)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y;
+    if (i >= a.ni || j >= a.nj) return;
+    const double *__restrict__ inf = a.inf.p + i * a.inf.si + j * a.inf.sj;
+    const double *__restrict__ diag = a.diag.p + i * a.diag.si + j * a.diag.sj;
+    double *__restrict__ sup = a.sup.p + i * a.sup.si + j * a.sup.sj;
+    double *__restrict__ rhs = a.rhs.p + i * a.rhs.si + j * a.rhs.sj;
+    double *__restrict__ out = a.out.p + i * a.out.si + j * a.out.sj;
+    const int nk = a.nk;
+
+    struct L { double inf, diag, sup, rhs; };
+    auto load = [&](int k) -> L {
+        L l = {0.0, 1.0, 0.0, 0.0};
+        if (k < nk) {
+            l.inf = __ldcs(inf + k * a.inf.sk);
+            l.diag = __ldcs(diag + k * a.diag.sk);
+            l.sup = __ldcs(sup + k * a.sup.sk);
+            l.rhs = __ldcs(rhs + k * a.rhs.sk);
+        }
+        return l;
+    };
+    L q[PF];
+#pragma unroll
+    for (int u = 0; u < PF; ++u) q[u] = load(u);
+    double sup_m1 = 0.0, rhs_m1 = 0.0;
+    for (int kb = 0; kb < nk; kb += PF) {
+#pragma unroll
+        for (int u = 0; u < PF; ++u) {
+            const int k = kb + u;
+            if (k < nk) {
+                L l = q[u];
+                q[u] = load(k + PF);
+                double s, r;
+                if (k == 0) {
+                    s = l.sup / l.diag;
+                    r = l.rhs / l.diag;
+                } else {
+                    s = l.sup / (l.diag - sup_m1 * l.inf);
+                    r = (l.rhs - l.inf * rhs_m1) / (l.diag - sup_m1 * l.inf);
+                }
+                sup[k * a.sup.sk] = s;
+                rhs[k * a.rhs.sk] = r;
+                sup_m1 = s;
+                rhs_m1 = r;
+            }
+        }
+    }
+    double o = rhs_m1;
+    __stcs(out + (int64_t)(nk - 1) * a.out.sk, o);
+    double qs[BPF], qr[BPF];
+    int top = nk - 2;
+#pragma unroll
+    for (int u = 0; u < BPF; ++u) {
+        const int k = top - u;
+        qs[u] = k >= 0 ? sup[k * a.sup.sk] : 0.0;
+        qr[u] = k >= 0 ? rhs[k * a.rhs.sk] : 0.0;
+    }
+    for (; top >= 0; top -= BPF) {
+#pragma unroll
+        for (int u = 0; u < BPF; ++u) {
+            const int k = top - u;
+            if (k >= 0) {
+                const double s = qs[u], r = qr[u];
+                const int kn = k - BPF;
+                qs[u] = kn >= 0 ? sup[kn * a.sup.sk] : 0.0;
+                qr[u] = kn >= 0 ? rhs[kn * a.rhs.sk] : 0.0;
+                o = r - s * o;
+                __stcs(out + k * a.out.sk, o);
+            }
+        }
+    }
+}
+
 }  // namespace b200
 
 extern "C" int b200_tridiag(const b200_field *inf, const b200_field *diag, const b200_field *sup,
@@ -95,12 +175,22 @@ extern "C" int b200_tridiag(const b200_field *inf, const b200_field *diag, const
     a.ni = (int)domain[0];
     a.nj = (int)domain[1];
     a.nk = (int)domain[2];
-    if (variant != 0 && variant != 1 && variant != 2) {
+    if (variant < 0 || variant > 7) {
         set_error("tridiag: unknown variant %d", variant);
         return B200_EUNSUP;
     }
     dim3 grid((a.ni + 127) / 128, a.nj, 1);
-    tridiag_column<4><<<grid, 128, 0, (cudaStream_t)stream>>>(a);
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (variant) {
+    case 1: tridiag_column<4><<<grid, 128, 0, st>>>(a); break;
+    case 2: tridiag_column_q<4, 4, 8><<<grid, 128, 0, st>>>(a); break;
+    case 3: tridiag_column_q<6, 4, 6><<<grid, 128, 0, st>>>(a); break;
+    case 4: tridiag_column_q<8, 8, 4><<<grid, 128, 0, st>>>(a); break;
+    case 5: tridiag_column_q<4, 8, 8><<<grid, 128, 0, st>>>(a); break;
+    case 6: tridiag_column_q<3, 4, 10><<<grid, 128, 0, st>>>(a); break;
+    case 7: tridiag_column_q<2, 4, 12><<<grid, 128, 0, st>>>(a); break;
+    default: tridiag_column_q<3, 4, 10><<<grid, 128, 0, st>>>(a); break;  // variant 0 = 6, the fastest measured
+    }
     B200_CUDA_CHECK(cudaGetLastError());
     return B200_OK;
 }

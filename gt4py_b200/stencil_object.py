@@ -456,7 +456,7 @@ class StencilObject:
         params = {name: kwargs[name] for name in cls._gt_parameter_info_}
         stream = current_stream()
         self._launch(_domain_, descs, params, stream)
-        if cls._device_sync_:
+        if cls._device_sync_ and not getattr(_tls, "capturing", False):
             if stream is None:
                 _lib.synchronize()
             else:
@@ -525,6 +525,64 @@ class use_stream:
     def __exit__(self, *exc):
         _tls.stream = self.prev
         return False
+
+
+class Graph:
+    """A sequence of stencil calls captured once into a CUDA graph and replayed with a single launch:
+
+        g = Graph()
+        with g:                              # nothing executes here: the launches are recorded
+            advect(phi, u, v, tmp, origin=..., domain=...)
+            diffuse(tmp, out, alpha=0.1, origin=..., domain=...)
+        for _ in range(steps):
+            g.launch()                       # one cudaGraphLaunch instead of two Python call paths
+        g.synchronize()
+
+    Field pointers, origins, domains and scalar parameters are baked in at capture time (call the stencils once
+    before capturing: their first call may allocate scratch and build caches).  Inside the capture the stencils'
+    `device_sync` is ignored.  The reference's callers pay `StencilObject.__call__` per stencil per step
+    (stencil_object.py:534-605); this is the call-path fusion of SURVEY.md 8(f) rank 2."""
+
+    def __init__(self, stream=None):
+        self.stream = stream if stream is not None else _lib.Stream()
+        self._exec = None
+        self._ctx = None
+
+    def __enter__(self):
+        if self._exec is not None:
+            raise RuntimeError("Graph: already captured")
+        self._ctx = use_stream(self.stream)
+        self._ctx.__enter__()
+        _lib.check(_lib.lib().b200_graph_begin(_lib.stream_handle(self.stream)))
+        _tls.capturing = True
+        return self
+
+    def __exit__(self, exc_type, exc, tb):
+        from ctypes import byref, c_void_p
+
+        _tls.capturing = False
+        handle = c_void_p()
+        rc = _lib.lib().b200_graph_end(_lib.stream_handle(self.stream), byref(handle))
+        self._ctx.__exit__(exc_type, exc, tb)
+        if exc_type is None:
+            _lib.check(rc)
+            self._exec = handle
+        return False
+
+    def launch(self, stream=None):
+        if self._exec is None:
+            raise RuntimeError("Graph: nothing captured")
+        _lib.check(_lib.lib().b200_graph_launch(self._exec, _lib.stream_handle(stream if stream is not None else self.stream)))
+
+    def synchronize(self):
+        _lib.check(_lib.lib().b200_stream_sync(_lib.stream_handle(self.stream)))
+
+    def __del__(self):
+        try:
+            if self._exec is not None:
+                _lib.lib().b200_graph_destroy(self._exec)
+        except Exception:
+            pass
 
 
 @dataclass(frozen=True)

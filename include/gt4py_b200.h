@@ -107,6 +107,16 @@ B200_API int b200_event_sync(void *event);
 B200_API int b200_event_elapsed_ms(void *start, void *stop, float *ms);
 B200_API int b200_stream_wait_event(void *stream, void *event);
 
+/* ---- CUDA graphs: capture a sequence of stencil launches once, replay it with one launch ----------
+ * The reference has no counterpart: its callers (model drivers) issue one StencilObject.__call__ per stencil
+ * (stencil_object.py:534-605, tens of microseconds of Python each); SURVEY.md 8(f) rank 2.
+ * b200_graph_begin puts `stream` into capture mode (relaxed: allocations stay legal); every b200_* launch on that
+ * stream is then recorded instead of executed.  b200_graph_end instantiates the executable graph. */
+B200_API int b200_graph_begin(void *stream);
+B200_API int b200_graph_end(void *stream, void **graph_exec);
+B200_API int b200_graph_launch(void *graph_exec, void *stream);
+B200_API int b200_graph_destroy(void *graph_exec);
+
 /* ---- hand-written hot stencils ------------------------------------------------------------ */
 /* variant: 0 = auto (fastest kernel whose layout preconditions hold), 1 = generic point kernel
  * (any strides), >= 2 = a specific tuned kernel (B200_EUNSUP if its preconditions fail).      */

@@ -66,7 +66,8 @@ def test_plan_is_loadable_without_gt4py(name):
     src = open(os.path.join(GEN, name, "kernel.cu")).read()
     for k in plan["kernels"]:
         assert f" {k['name']}(const Args a)" in src and f" {k['name']}_u(const Args a)" in src
-    assert (name.split("__")[0] in LIBRARY_MATCHED) == ("library" in plan)
+    # float32 re-annotations must NOT match the (float64) library kernels
+    assert (name.split("__")[0] in LIBRARY_MATCHED and not name.endswith("__f32")) == ("library" in plan)
 
 
 def test_argument_block_layout_matches_c(tmp_path):

@@ -79,13 +79,29 @@ def test_vadv_golden(path, variant):
     assert np.array_equal(out, g["utens_stage"])
 
 
+@pytest.mark.parametrize("variant", [0, 1, 2])
 @pytest.mark.parametrize("path", _cases("tridiag"), ids=os.path.basename)
-def test_tridiag_golden(path):
+def test_tridiag_golden(path, variant):
     g = np.load(path)
     dom = tuple(int(x) for x in g["shape"])
     f = gen.tridiag_inputs(*dom, seed=int(g["seed"]))
     d = {k: _dev(v, (0, 0, 0)) for k, v in f.items()}
-    stencils.tridiagonal_solver(d["inf"], d["diag"], d["sup"], d["rhs"], d["out"], domain=dom)
+    st = stencils.TridiagonalSolver.with_variant(variant)
+    st(d["inf"], d["diag"], d["sup"], d["rhs"], d["out"], domain=dom)
+    for name in ("sup", "rhs", "out"):
+        assert np.array_equal(d[name].asnumpy(), g[name]), name
+
+
+@pytest.mark.parametrize("variant", [1, 2, 3, 4, 5, 6, 7])
+@pytest.mark.parametrize("dom", [(128, 64, 80), (61, 59, 5), (1, 1, 2), (129, 3, 9), (33, 17, 8), (40, 5, 17),
+                                 (300, 2, 16), (7, 7, 81)])
+def test_tridiag_vs_oracle(dom, variant):
+    """ragged sizes around the prefetch depth (8) of the forward and the backward sweep"""
+    f = gen.tridiag_inputs(*dom, seed=77)
+    d = {k: _dev(v, (0, 0, 0)) for k, v in f.items()}
+    stencils.TridiagonalSolver.with_variant(variant)(d["inf"], d["diag"], d["sup"], d["rhs"], d["out"], domain=dom)
+    g = {k: v.copy() for k, v in f.items()}
+    oracle.tridiag(g["inf"], g["diag"], g["sup"], g["rhs"], g["out"], domain=dom)
     for name in ("sup", "rhs", "out"):
         assert np.array_equal(d[name].asnumpy(), g[name]), name
 
@@ -248,3 +264,56 @@ def test_host_pipeline_matches_oracle(chunks):
     assert np.array_equal(host["utens_stage"], ref)
     for v in host.values():
         storage.free_pinned(v)
+
+
+# ---- CUDA-graph replay of a captured call sequence (gt4py_b200.Graph) -------------------------------------------
+def test_graph_replay_matches_direct_calls():
+    """hdiff + vadv + a generated stencil captured once, replayed on new field contents (same buffers)."""
+    from gt4py_b200 import generated
+
+    dom = (48, 40, 12)
+    hf = gen.hdiff_inputs(*dom, seed=11)
+    vf = gen.vadv_inputs(*dom, seed=12)
+    h = {k: _dev(v, (2, 2, 0)) for k, v in hf.items()}
+    v = {k: _dev(a, (0, 0, 0)) for k, a in vf.items() if k != "dtr_stage"}
+    chain_dir = os.path.join(GOLDEN, "generated", "fv3_chain")
+    st_chain = generated.load_plan(chain_dir)
+    rng = np.random.default_rng(5)
+    cf = {k: rng.uniform(-1.0, 1.5, (dom[0] + 6, dom[1] + 6, dom[2])) for k in ("phi", "u", "v")}
+    c = {k: _dev(a, (3, 3, 0)) for k, a in cf.items()}
+    c_out = storage.zeros(dom)
+    hd, va = stencils.HorizontalDiffusion(), stencils.VerticalAdvectionDycore()
+
+    def sequence():
+        hd(h["in_field"], h["out_field"], h["coeff"], origin=(2, 2, 0), domain=dom)
+        va(v["utens_stage"], v["u_stage"], v["wcon"], v["u_pos"], v["utens"], dtr_stage=vf["dtr_stage"],
+           origin=(0, 0, 0), domain=dom)
+        st_chain(c["phi"], c["u"], c["v"], c_out, dt=0.05, alpha=0.03,
+                 origin={"_all_": (3, 3, 0), "out": (0, 0, 0)}, domain=dom)
+
+    sequence()  # warm-up: scratch allocation, module load, descriptor caches
+    gb.synchronize()
+    v["utens_stage"].set(vf["utens_stage"])  # vadv updates it in place
+    g = gb.Graph()
+    with g:
+        sequence()
+    for trial in range(3):
+        hf2 = gen.hdiff_inputs(*dom, seed=20 + trial)
+        vf2 = gen.vadv_inputs(*dom, seed=30 + trial)
+        h["in_field"].set(hf2["in_field"])
+        h["coeff"].set(hf2["coeff"])
+        for k in ("utens_stage", "u_stage", "wcon", "u_pos", "utens"):
+            v[k].set(vf2[k])
+        phi2 = rng.uniform(-1.0, 1.5, cf["phi"].shape)
+        c["phi"].set(phi2)
+        gb.synchronize()
+        g.launch()
+        g.synchronize()
+        ref_h = oracle.hdiff(hf2["in_field"], hf2["out_field"].copy(), hf2["coeff"], domain=dom)
+        assert np.array_equal(h["out_field"].asnumpy(), ref_h)
+        ref_v = oracle.vadv(vf2["utens_stage"].copy(), vf2["u_stage"], vf2["wcon"], vf2["u_pos"], vf2["utens"],
+                            dtr_stage=vf["dtr_stage"], domain=dom)
+        assert np.array_equal(v["utens_stage"].asnumpy(), ref_v)
+        from oracle import chain
+
+        assert np.array_equal(c_out.asnumpy(), chain.fv3_chain(phi2, cf["u"], cf["v"], 0.05, 0.03))

@@ -80,6 +80,20 @@ def definitions():
         defs[name + "__tile"] = (*defs[name][:2], {"fuse_temporaries": True})
     for name in ("fv3_chain", "exec_info_diffusion"):
         defs[name + "__point"] = (*defs[name][:2], {"fuse_temporaries": False})
+    # float32 variants of the headline stencils (north_star tolerance for float32: 1e-5; these are bit-exact):
+    # the same definitions re-annotated the way the reference's suites do it (testing/utils.py:24-30)
+    import inspect
+
+    import numpy as np
+    from gt4py.cartesian import gtscript
+    from gt4py.cartesian.testing.utils import annotate_function
+
+    for name in ("horizontal_diffusion", "vertical_advection_dycore", "tridiagonal_solver", "fv3_chain"):
+        fn, ext = defs[name][:2]
+        spec = inspect.getfullargspec(fn)
+        dtypes = {a: gtscript.Field[np.float32] for a in spec.args}
+        dtypes.update({a: np.float32 for a in spec.kwonlyargs})
+        defs[name + "__f32"] = (annotate_function(fn, dtypes), ext)
     return defs
 
 
@@ -90,7 +104,8 @@ def main():
 
     defs = definitions()
     names = sys.argv[1:] or sorted(defs)
-    report = {}
+    report_path = os.path.join(OUT, "REPORT.json")
+    report = json.load(open(report_path)) if sys.argv[1:] and os.path.exists(report_path) else {}
     for name in names:
         fn, ext, *opts = defs[name]
         opts = opts[0] if opts else {}
@@ -130,7 +145,7 @@ def main():
             plan = json.load(fh)
         report[name] = "ok: " + ", ".join(f"{k['name']}:{k['kind']}" for k in plan["kernels"])
         print("ok  ", name, report[name])
-    with open(os.path.join(OUT, "REPORT.json"), "w") as fh:
+    with open(report_path, "w") as fh:
         json.dump(report, fh, indent=1, sort_keys=True)
 
 
