@@ -107,6 +107,7 @@ _PROTOTYPES = {
     "b200_event_record": ([_VP, _VP], c_int),
     "b200_event_sync": ([_VP], c_int),
     "b200_event_elapsed_ms": ([_VP, _VP, POINTER(c_float)], c_int),
+    "b200_tmap_encode": ([POINTER(Field), POINTER(c_uint32), _VP, POINTER(c_int32)], c_int),
     "b200_graph_begin": ([_VP], c_int),
     "b200_graph_end": ([_VP, POINTER(_VP)], c_int),
     "b200_graph_launch": ([_VP, _VP], c_int),

@@ -280,3 +280,56 @@ int encode_tmap_f64(CUtensorMap *map, const double *base, const int64_t extent[3
     return B200_OK;
 }
 }  // namespace b200
+
+
+extern "C" int b200_tmap_encode(const b200_field *f, const uint32_t box[3], void *tmap128, int32_t *i_shift)
+{
+    using namespace b200;
+    B200_REQUIRE(f && f->ptr && box && tmap128 && i_shift, "tmap_encode: bad arguments");
+    B200_REQUIRE(f->ndim >= 3, "tmap_encode: field needs the I, J, K axes");
+    CUtensorMapDataType dt;
+    int item;
+    switch (f->dtype) {
+    case B200_FLOAT64: dt = CU_TENSOR_MAP_DATA_TYPE_FLOAT64; item = 8; break;
+    case B200_FLOAT32: dt = CU_TENSOR_MAP_DATA_TYPE_FLOAT32; item = 4; break;
+    case B200_INT64: dt = CU_TENSOR_MAP_DATA_TYPE_INT64; item = 8; break;
+    case B200_INT32: dt = CU_TENSOR_MAP_DATA_TYPE_INT32; item = 4; break;
+    default: set_error("tmap_encode: dtype %d has no TMA element type", f->dtype); return B200_EUNSUP;
+    }
+    const int64_t sj = f->stride[1] * item, sk = f->stride[2] * item;
+    const uintptr_t misalign = (uintptr_t)f->ptr & 15;
+    if (f->stride[0] != 1 || misalign % item || sj % 16 || sk % 16 || sj <= 0 || sk <= 0 ||
+        (box[0] * item) % 16 || box[0] > 256 || box[1] > 256 || box[2] > 256 || !box[0] || !box[1] || !box[2]) {
+        set_error("tmap_encode: layout not TMA-compatible (stride_i %lld, byte strides %lld / %lld, box %u x %u x %u)",
+                  (long long)f->stride[0], (long long)sj, (long long)sk, box[0], box[1], box[2]);
+        return B200_EUNSUP;
+    }
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        B200_CUDA_CHECK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q));
+        if (q != cudaDriverEntryPointSuccess || !p) {
+            set_error("cuTensorMapEncodeTiled is not available in this driver");
+            return B200_ECUDA;
+        }
+        fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    const int shift = (int)(misalign / item);  // the bytes below the base belong to the same (256-byte aligned) allocation
+    void *base = (char *)f->ptr - misalign;
+    *i_shift = shift;
+    cuuint64_t dims[3] = {(cuuint64_t)(f->shape[0] + shift), (cuuint64_t)f->shape[1], (cuuint64_t)f->shape[2]};
+    cuuint64_t strides[2] = {(cuuint64_t)sj, (cuuint64_t)sk};
+    cuuint32_t bx[3] = {box[0], box[1], box[2]};
+    cuuint32_t es[3] = {1, 1, 1};
+    alignas(64) CUtensorMap map;
+    CUresult r = fn(&map, dt, 3, base, dims, strides, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+        return B200_ECUDA;
+    }
+    static_assert(sizeof(CUtensorMap) == 128, "CUtensorMap is 128 bytes");
+    memcpy(tmap128, &map, 128);
+    return B200_OK;
+}

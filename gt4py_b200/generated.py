@@ -60,11 +60,16 @@ class _Module:
 
 
 def _args_struct(plan):
+    """ctypes mirror of the generated `struct Args`."""
     fields = []
     for name, kind, dtype, nstr in plan["args"]:
         if kind == "field":
             fields.append((name, c_void_p))
             fields.append((name + "_s", ctypes.c_int64 * nstr))
+        elif kind == "tmap":
+            fields.append((name, c_void_p))  # device address of a CUtensorMap
+        elif kind == "origin":
+            fields.append((name, ctypes.c_int32 * 3))
         else:
             fields.append((name, _CT[dtype]))
     fields += [("ni", ctypes.c_int32), ("nj", ctypes.c_int32), ("nk", ctypes.c_int32)]
@@ -82,12 +87,14 @@ class GeneratedStencil(StencilObject):
     def _module(cls):
         if cls.__dict__.get("_mod") is None:
             cubin = compile_cubin(os.path.join(cls._dir_, cls._plan_.get("source", "kernel.cu")))
-            names = [k["name"] + sfx for k in cls._plan_["kernels"] for sfx in ("", "_u")]
+            names = [k["name"] + sfx for k in cls._plan_["kernels"] for sfx in ("", "_u") + (("_t",) if "tma" in k else ())]
             cls._mod = _Module(cubin, names)
             for k in cls._plan_["kernels"]:
-                if k.get("smem_bytes", 0) > 48 * 1024:  # opt in to more than the default dynamic shared memory
-                    for sfx in ("", "_u"):
-                        _lib.check(_lib.lib().b200_kernel_set_smem(cls._mod.kernels[k["name"] + sfx], int(k["smem_bytes"])))
+                for sfx, nbytes in (("", k.get("smem_bytes", 0)), ("_u", k.get("smem_bytes", 0)),
+                                    ("_t", k.get("tma", {}).get("smem_bytes", 0))):
+                    if nbytes > 48 * 1024:  # opt in to more than the default dynamic shared memory
+                        _lib.check(_lib.lib().b200_kernel_set_smem(cls._mod.kernels[k["name"] + sfx], int(nbytes)))
+            cls._tmaps = {}
             cls._Args = _args_struct(cls._plan_)
             cls._scratch = {}
         return cls._mod
@@ -166,7 +173,44 @@ class GeneratedStencil(StencilObject):
             unit = unit and (strides[0] in (0, 1))
         for s in cls._plan_["scalars"]:
             setattr(a, s["name"], params[s["name"]])
+        # TMA descriptors of the staged inputs (cached per field layout); a field that is not TMA-compatible
+        # (alignment, strides) sends its kernel to the plain entry point instead
+        tma_ok = {}
+        if unit and os.environ.get("B200_GENERATED_TMA", "1") != "0":
+            shifts = {}
+            for name, kind, fname, extra in cls._plan_["args"]:
+                if kind != "tmap":
+                    continue
+                f = fields[fname]
+                key = (name, f.ptr, tuple(f.shape[:3]), tuple(f.stride[:3]))
+                hit = cls._tmaps.get(key)
+                if hit is None:
+                    blob, shift = (ctypes.c_uint8 * 128)(), ctypes.c_int32(0)
+                    rc = _lib.lib().b200_tmap_encode(byref(f), (ctypes.c_uint32 * 3)(*extra["box"]), blob, byref(shift))
+                    if rc == -3:  # B200_EUNSUP: layout not TMA-compatible
+                        hit = False
+                    else:
+                        _lib.check(rc)
+                        dev = storage._Buffer(128)  # the descriptor lives in global memory (256-byte aligned)
+                        _lib.check(_lib.lib().b200_memcpy_h2d(c_void_p(dev.ptr), blob, 128, None))
+                        hit = (dev, int(shift.value))
+                    if len(cls._tmaps) > 64:
+                        cls._tmaps.clear()
+                    cls._tmaps[key] = hit
+                kname = extra["kernel"]
+                if hit is False:
+                    tma_ok[kname] = False
+                else:
+                    setattr(a, name, hit[0].ptr)
+                    shifts[fname] = hit[1]
+                    tma_ok.setdefault(kname, True)
+            for name, kind, fname, extra in cls._plan_["args"]:
+                if kind == "origin":  # array index of the compute origin, in the descriptor's coordinates
+                    org = [int(x) for x in fields[fname].origin[:3]]
+                    org[0] += shifts.get(fname, 0)
+                    getattr(a, name)[:] = org
         ni, nj, nk = domain
+        cls._last_entry_points = []  # what the last call launched (tests check that the intended variant ran)
         argp = (c_void_p * 1)(ctypes.cast(byref(a), c_void_p))
         sh = _lib.stream_handle(stream)
         for k in cls._plan_["kernels"]:
@@ -174,17 +218,20 @@ class GeneratedStencil(StencilObject):
             wj = nj + k["j_ext"][1] - k["j_ext"][0]
             if wi <= 0 or wj <= 0:
                 continue
-            smem = 0
+            smem, sfx = 0, ("_u" if unit else "")
             if k["kind"] == "point":
                 block, grid = (64, 4, 1), ((wi + 63) // 64, (wj + 3) // 4, nk)
             elif k["kind"] == "tile":  # a CTA per TI x TJ tile of the compute domain and level; halo recomputed
                 ti, tj = k["tile"]
                 block, grid, smem = (*k["block"], 1), ((ni + ti - 1) // ti, (nj + tj - 1) // tj, nk), k["smem_bytes"]
+                if tma_ok.get(k["name"]):
+                    sfx, smem = "_t", k["tma"]["smem_bytes"]
             else:
                 block, grid = (32, 4, 1), ((wi + 31) // 32, (wj + 3) // 4, 1)
             if nk <= 0 and k["kind"] != "column":
                 continue
-            _lib.check(_lib.lib().b200_launch(mod.kernels[k["name"] + ("_u" if unit else "")], (ctypes.c_uint32 * 3)(*grid),
+            cls._last_entry_points.append(k["name"] + sfx)
+            _lib.check(_lib.lib().b200_launch(mod.kernels[k["name"] + sfx], (ctypes.c_uint32 * 3)(*grid),
                                               (ctypes.c_uint32 * 3)(*block), smem, sh, argp, 1))
 
 

@@ -146,6 +146,15 @@ B200_API int b200_module_load(const void *image, size_t bytes, void **module);
 B200_API int b200_module_unload(void *module);
 B200_API int b200_module_get_kernel(void *module, const char *name, void **kernel);
 B200_API int b200_kernel_set_smem(void *kernel, int dynamic_smem_bytes);
+/* A 128-byte TMA descriptor (CUtensorMap, cuTensorMapEncodeTiled) over the I, J, K axes of `field` -- the whole
+ * allocation, so tile coordinates are array indices (origin + offset) and out-of-range parts of a box are
+ * zero-filled by the hardware.  The generated tile kernels take it inside their argument block and stage the
+ * halo'd input tiles in shared memory with cp.async.bulk.tensor.  box = tile extent per axis (<= 256 each).
+ * Needs unit I stride and J / K strides that are multiples of 16 bytes; otherwise B200_EUNSUP (the caller then
+ * launches the non-TMA entry point of the same kernel).  TMA wants a 16-byte aligned base: when the array starts
+ * 4 / 8 / 12 bytes off (gt4py.storage aligns the ORIGIN, so an odd halo leaves the base misaligned) the descriptor
+ * starts at the aligned address below it and *i_shift receives the number of elements to add to I coordinates. */
+B200_API int b200_tmap_encode(const b200_field *field, const uint32_t box[3], void *tmap128, int32_t *i_shift);
 /* args: array of nargs pointers to the argument values (cudaLaunchKernel convention). */
 B200_API int b200_launch(void *kernel, const uint32_t grid[3], const uint32_t block[3],
                 uint32_t dynamic_smem_bytes, void *stream, void **args, int nargs);

@@ -272,3 +272,33 @@ def test_fv3_chain_against_the_oracle_at_other_sizes(domain):
     out = storage.zeros((ni, nj, nk))
     st(d["phi"], d["u"], d["v"], out, dt=0.05, alpha=0.03, origin={"_all_": (h, h, 0), "out": (0, 0, 0)}, domain=domain)
     assert np.array_equal(out.asnumpy(), want)
+    assert type(st)._last_entry_points == ["k0_0_t"]  # the TMA-staged entry point (odd halo: base 8 bytes off)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["tma", "unit", "generic"])
+def test_fv3_chain_entry_points_agree(mode, monkeypatch):
+    """the three entry points of the tile kernel (<k>_t TMA-staged, <k>_u unit stride, <k> any strides)"""
+    from gt4py_b200 import storage
+    from oracle import chain
+
+    ni, nj, nk = domain = (70, 37, 4)
+    rng = np.random.default_rng(3)
+    h = chain.HALO
+    host = {k: rng.uniform(-1.0, 1.5, (ni + 2 * h, nj + 2 * h, nk)) for k in ("phi", "u", "v")}
+    want = chain.fv3_chain(host["phi"], host["u"], host["v"], 0.05, 0.03)
+    if mode == "unit":
+        monkeypatch.setenv("B200_GENERATED_TMA", "0")
+    st = generated.load_plan(os.path.join(GEN, "fv3_chain"))
+    if mode == "generic":  # K-fastest storage viewed as (I, J, K): stride_I != 1
+        d = {k: storage.from_array(np.ascontiguousarray(a.transpose(2, 1, 0))).transpose(2, 1, 0) for k, a in host.items()}
+    else:
+        d = {k: storage.from_array(a, aligned_index=(h, h, 0)) for k, a in host.items()}
+    out = storage.zeros((ni, nj, nk))
+    import warnings
+
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")  # non-optimal layout warning for the transposed fields
+        st(d["phi"], d["u"], d["v"], out, dt=0.05, alpha=0.03, origin={"_all_": (h, h, 0), "out": (0, 0, 0)}, domain=domain)
+    assert np.array_equal(out.asnumpy(), want)
+    assert type(st)._last_entry_points == [{"tma": "k0_0_t", "unit": "k0_0_u", "generic": "k0_0"}[mode]]
