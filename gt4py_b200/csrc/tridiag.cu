@@ -153,6 +153,11 @@ __global__ void __launch_bounds__(128, MINB) tridiag_column_q(TriArgs a)
     }
 }
 
+// tridiag_fused.cu: TMA ring + Tensor-Memory LIFO, fused sweeps
+int launch_tridiag_fused(const View3<const double> &inf, const View3<const double> &diag, const View3<double> &sup,
+                         const View3<double> &rhs, const View3<double> &out, int ni, int nj, int nk,
+                         cudaStream_t stream, bool *handled);
+
 }  // namespace b200
 
 extern "C" int b200_tridiag(const b200_field *inf, const b200_field *diag, const b200_field *sup,
@@ -175,12 +180,21 @@ extern "C" int b200_tridiag(const b200_field *inf, const b200_field *diag, const
     a.ni = (int)domain[0];
     a.nj = (int)domain[1];
     a.nk = (int)domain[2];
-    if (variant < 0 || variant > 7) {
+    if (variant < 0 || variant > 8) {
         set_error("tridiag: unknown variant %d", variant);
         return B200_EUNSUP;
     }
     dim3 grid((a.ni + 127) / 128, a.nj, 1);
     cudaStream_t st = (cudaStream_t)stream;
+    if (variant == 0 || variant == 8) {  // fused TMEM kernel when the layout allows it (tridiag_fused.cu)
+        bool handled = false;
+        if ((rc = launch_tridiag_fused(a.inf, a.diag, a.sup, a.rhs, a.out, a.ni, a.nj, a.nk, st, &handled))) return rc;
+        if (handled) return B200_OK;
+        if (variant == 8) {
+            set_error("tridiag variant 8 (fused TMEM kernel) needs TMA-compatible fields and nk >= 2");
+            return B200_EUNSUP;
+        }
+    }
     switch (variant) {
     case 1: tridiag_column<4><<<grid, 128, 0, st>>>(a); break;
     case 2: tridiag_column_q<4, 4, 8><<<grid, 128, 0, st>>>(a); break;

@@ -79,7 +79,7 @@ def test_vadv_golden(path, variant):
     assert np.array_equal(out, g["utens_stage"])
 
 
-@pytest.mark.parametrize("variant", [0, 1, 2])
+@pytest.mark.parametrize("variant", [0, 1, 2, 8])
 @pytest.mark.parametrize("path", _cases("tridiag"), ids=os.path.basename)
 def test_tridiag_golden(path, variant):
     g = np.load(path)
@@ -92,14 +92,19 @@ def test_tridiag_golden(path, variant):
         assert np.array_equal(d[name].asnumpy(), g[name]), name
 
 
-@pytest.mark.parametrize("variant", [1, 2, 3, 4, 5, 6, 7])
+@pytest.mark.parametrize("variant", [0, 1, 2, 3, 4, 5, 6, 7, 8])
 @pytest.mark.parametrize("dom", [(128, 64, 80), (61, 59, 5), (1, 1, 2), (129, 3, 9), (33, 17, 8), (40, 5, 17),
-                                 (300, 2, 16), (7, 7, 81)])
+                                 (300, 2, 16), (7, 7, 81), (256, 300, 2), (70, 9, 127), (130, 66, 128), (64, 8, 131)])
 def test_tridiag_vs_oracle(dom, variant):
     """ragged sizes around the prefetch depth (8) of the forward and the backward sweep"""
     f = gen.tridiag_inputs(*dom, seed=77)
     d = {k: _dev(v, (0, 0, 0)) for k, v in f.items()}
-    stencils.TridiagonalSolver.with_variant(variant)(d["inf"], d["diag"], d["sup"], d["rhs"], d["out"], domain=dom)
+    try:
+        stencils.TridiagonalSolver.with_variant(variant)(d["inf"], d["diag"], d["sup"], d["rhs"], d["out"], domain=dom)
+    except gb.B200Error as exc:
+        if exc.code == -3 and variant == 8:  # B200_EUNSUP: the fused kernel's preconditions fail
+            pytest.skip(str(exc))
+        raise
     g = {k: v.copy() for k, v in f.items()}
     oracle.tridiag(g["inf"], g["diag"], g["sup"], g["rhs"], g["out"], domain=dom)
     for name in ("sup", "rhs", "out"):
