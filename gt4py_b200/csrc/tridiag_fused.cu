@@ -289,7 +289,7 @@ static int launch_tri(const TriFArgs &a, cudaStream_t stream, bool *handled)
     const size_t lifo = (size_t)(nstages - nTs) * 2 * TK * VM_COLS * 8;
     const long avail = (long)max_smem - VM_BAR_BYTES - (long)lifo;
     int S = avail > 0 ? (int)(avail / G::SLOT_F) : 0;
-    const int want = env_s > 0 ? env_s : 8;
+    const int want = env_s > 0 ? env_s : 4;  // measured at 1024x1024x80: S = 4 0.73 ms, 3 0.77, 5 0.76, 8 0.83 (deeper rings lose DRAM locality)
     if (S > want) S = want;
     if (S > VM_MAX_STAGES) S = VM_MAX_STAGES;
     if (S < 2) return B200_OK;  // LIFO does not fit on chip: not handled here
