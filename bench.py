@@ -359,7 +359,7 @@ def run_b200(args):
                 "traffic": TRAFFIC.get(name), "ms_per_launch": round(t_ms, 4),
                 "alg_bytes_per_launch": n * ALG_BYTES[name], "peak_source": peak_src}
 
-    kernels = {"hdiff": roof("hdiff", t_h, "hdiff_jmarch"), "vadv": roof("vadv", t_v, "vadv_fused2_kernel")}
+    kernels = {"hdiff": roof("hdiff", t_h, "hdiff_tma_kernel"), "vadv": roof("vadv", t_v, "vadv_fused2_kernel")}
     dominant = "vadv" if t_v >= t_h else "hdiff"
 
     # ---- e2e: host buffers in, host buffers out, every step (public API) ----------------------------

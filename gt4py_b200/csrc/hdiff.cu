@@ -13,7 +13,7 @@
 //                   neighbours with warp shuffles.  Every in_field element is loaded once per
 //                   J-strip; the 4 overlap columns/rows between neighbouring warps/strips are L1/L2
 //                   hits, so DRAM traffic stays at ~24 B/point (8 in + 8 coeff + 8 out).
-#include "common.cuh"
+#include "hdiff.cuh"
 
 namespace b200 {
 
@@ -282,7 +282,14 @@ static int launch_hdiff(View3<const double> in, View3<double> out, View3<const d
                          aligned16(out.p) && aligned16(co.p) && (in.sj % 2 == 0) &&
                          (in.sk % 2 == 0) && (out.sj % 2 == 0) && (out.sk % 2 == 0) &&
                          (co.sj % 2 == 0) && (co.sk % 2 == 0);
-    if (variant == 0) variant = fast_ok ? 2 : 1;
+    if (variant == 0) {  // auto: TMA-ring kernel, else the register J-march, else the point kernel
+        if (fast_ok) {
+            bool handled = false;
+            int rc = launch_hdiff_tma(LIMITER, in, out, co, ni, nj, nk, stream, &handled);
+            if (rc != B200_OK || handled) return rc;
+        }
+        variant = fast_ok ? 2 : 1;
+    }
     if (variant == 1) {
         dim3 block(64, 4, 1);
         dim3 grid((ni + 63) / 64, (nj + 3) / 4, nk);
@@ -311,6 +318,15 @@ static int launch_hdiff(View3<const double> in, View3<double> out, View3<const d
             hdiff_jmarch<LIMITER, 4><<<grid, block, 0, stream>>>(in, out, co, ni, nj, nk, tj);
         else  // variant 4: alternating march directions (less DRAM traffic, not faster: see DESIGN.md 3.1)
             hdiff_jmarch_alt<LIMITER, 2, 4><<<grid, block, 0, stream>>>(in, out, co, ni, nj, nk, tj);
+    } else if (variant == 5) {
+        bool handled = false;
+        int rc = launch_hdiff_tma(LIMITER, in, out, co, ni, nj, nk, stream, &handled);
+        if (rc != B200_OK) return rc;
+        if (!handled) {
+            set_error("hdiff variant 5 needs unit I stride, 16-byte aligned origins and even J/K strides");
+            return B200_EUNSUP;
+        }
+        return B200_OK;
     } else {
         set_error("hdiff: unknown variant %d", variant);
         return B200_EUNSUP;

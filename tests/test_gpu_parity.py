@@ -52,7 +52,7 @@ def run_vadv(f, domain, variant):
     return d["utens_stage"].asnumpy()
 
 
-@pytest.mark.parametrize("variant", [1, 2, 3, 4])
+@pytest.mark.parametrize("variant", [1, 2, 3, 4, 5])
 @pytest.mark.parametrize("path", _cases("hdiff"), ids=os.path.basename)
 def test_hdiff_golden(path, variant):
     g = np.load(path)
@@ -61,7 +61,7 @@ def test_hdiff_golden(path, variant):
     assert np.array_equal(out, g["out_field"])  # halo of out_field must stay untouched (zeros)
 
 
-@pytest.mark.parametrize("variant", [1, 2, 4])
+@pytest.mark.parametrize("variant", [1, 2, 4, 5])
 @pytest.mark.parametrize("path", _cases("simple_hdiff"), ids=os.path.basename)
 def test_simple_hdiff_golden(path, variant):
     g = np.load(path)
@@ -111,9 +111,9 @@ def test_tridiag_vs_oracle(dom, variant):
         assert np.array_equal(d[name].asnumpy(), g[name]), name
 
 
-@pytest.mark.parametrize("variant", [0, 1, 2, 3, 4])
+@pytest.mark.parametrize("variant", [0, 1, 2, 3, 4, 5])
 @pytest.mark.parametrize("dom", [(128, 128, 80), (61, 59, 5), (60, 8, 1), (121, 33, 2), (2, 2, 2),
-                                 (300, 7, 3), (64, 100, 3), (17, 65, 2)])
+                                 (300, 7, 3), (64, 100, 3), (17, 65, 2), (241, 130, 2), (180, 257, 1)])
 def test_hdiff_vs_oracle(dom, variant):
     f = gen.hdiff_inputs(*dom, seed=123)
     ref = oracle.hdiff(f["in_field"], f["out_field"].copy(), f["coeff"], domain=dom)

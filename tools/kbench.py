@@ -55,6 +55,10 @@ def main():
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--sets", type=int, default=3)
+    ap.add_argument("--sweep", default="", help="environment sweep, e.g. 'B200_HDIFF_NW=2,3;B200_HDIFF_NS=3,4' "
+                    "(cartesian product; the launchers read these hooks at every call)")
+    ap.add_argument("--check", type=int, default=-1, help="compare each run's output of set 0 bit-for-bit with "
+                    "this variant's (hdiff: out_field, vadv: utens_stage needs fresh inputs -> hdiff only)")
     a = ap.parse_args()
     ni, nj, nk = a.shape
     dom = (ni, nj, nk)
@@ -62,7 +66,18 @@ def main():
            "tridiag": stencils.TridiagonalSolver}[a.stencil]
     sets = make_sets(a.stencil, ni, nj, nk, a.sets)
     n = ni * nj * nk
-    for v in a.variants:
+    import itertools
+
+    axes = [(kv.split("=")[0], kv.split("=")[1].split(",")) for kv in a.sweep.split(";") if kv]
+    combos = [dict(zip([k for k, _ in axes], vals)) for vals in itertools.product(*[v for _, v in axes])] or [{}]
+    ref_out = None
+    if a.check >= 0 and a.stencil == "hdiff":
+        st = cls.with_variant(a.check)
+        call(a.stencil, st, sets[0], dom)
+        synchronize()
+        ref_out = sets[0]["out_field"].asnumpy().copy()
+    for v, env in itertools.product(a.variants, combos):
+        os.environ.update(env)
         st = cls.with_variant(v)
         type(st).configure(device_sync=False)
         for it in range(a.warmup):
@@ -76,7 +91,10 @@ def main():
         synchronize()
         ms = np.array([s.elapsed_ms(e) for s, e in evs])
         best, med = float(ms.min()), float(np.median(ms))
-        print(json.dumps({"stencil": a.stencil, "shape": dom, "variant": v, "ms_min": round(best, 4),
+        extra = dict(env)
+        if ref_out is not None:
+            extra["bit_exact"] = bool(np.array_equal(sets[0]["out_field"].asnumpy(), ref_out))
+        print(json.dumps({"stencil": a.stencil, "shape": dom, "variant": v, **extra, "ms_min": round(best, 4),
                           "ms_median": round(med, 4), "gpts_s_median": round(n / med / 1e6, 2),
                           "alg_GBs_median": round(n * ALG_BYTES[a.stencil] / med / 1e6, 1),
                           "alg_GBs_best": round(n * ALG_BYTES[a.stencil] / best / 1e6, 1)}), flush=True)
