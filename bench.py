@@ -206,6 +206,52 @@ def run_reference(args):
     return 0
 
 
+def bind_near_gpu(index: int):
+    """Pin this rank to the host cores NVML reports as closest to its GPU (intersected with the cores this
+    process may use), so that the pinned host buffers of the e2e path are first-touched on the GPU's NUMA node.
+    Returns a short description for the JSON line; never fatal."""
+    try:
+        import pynvml
+
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        allowed = os.sched_getaffinity(0)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (max(allowed) // 64) + 1)
+        near = {64 * w + b for w, word in enumerate(words) for b in range(64) if (int(word) >> b) & 1}
+        pick = sorted(near & allowed)
+        if pick and len(pick) < len(allowed):
+            os.sched_setaffinity(0, pick)
+            return f"bound to {len(pick)} of {len(allowed)} allowed cores near GPU {index}"
+        return f"{len(allowed)} allowed cores, all equally near GPU {index}" if pick else "GPU-near cores not allowed"
+    except Exception as exc:  # NVML missing / restricted container
+        return f"unbound ({type(exc).__name__})"
+
+
+def halo_leg(halo, sets, stream, gb, barrier, allmax, reps=50):
+    """The halo exchange alone: `reps` x (wcon refresh + in_field refresh) back to back on one stream, CUDA
+    events, max over ranks.  Bytes are what one GPU receives over NVLink per step."""
+    nbytes = halo.bytes_received(0) + halo.bytes_received(1)
+    for i in range(5):
+        halo.refresh(2 * (i % sets) + 1, stream)
+        halo.refresh(2 * (i % sets), stream)
+    barrier()
+    e0, e1 = gb.Event(), gb.Event()
+    e0.record(stream)
+    for i in range(reps):
+        halo.refresh(2 * (i % sets) + 1, stream)
+        halo.refresh(2 * (i % sets), stream)
+    e1.record(stream)
+    stream.synchronize()
+    us = allmax(e0.elapsed_ms(e1)) * 1e3 / reps
+    barrier()
+    gbs = nbytes / us / 1e3
+    return {"bytes_received_per_gpu_per_step": int(nbytes), "us_per_step": round(us, 2), "achieved": round(gbs, 1),
+            "unit": "GB/s", "peak": 900.0, "frac": round(gbs / 900.0, 4),
+            "peak_source": "NVLink 5 nominal, per direction per GPU (B200_PROFILING.md; measured peer copy 770 GB/s)",
+            "note": "faces of 1.3-2.6 MB and 2.5 KB corners: launch/flag latency, not link bandwidth, bounds it",
+            "launches_counted": (5 + reps) * 2 * halo.launches_per_refresh}
+
+
 # ---- the b200 arm ------------------------------------------------------------------------------------
 def run_b200(args):
     rank = int(os.environ.get("RANK", "0"))
@@ -220,12 +266,19 @@ def run_b200(args):
             return subprocess.call(cmd)
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
 
+    # libraries (NCCL prints its version banner) must not write into the one-JSON-line stdout contract:
+    # everything written to fd 1 from here on goes to stderr, the result line goes to the saved descriptor
+    sys.stdout.flush()
+    result_fd = os.dup(1)
+    os.dup2(2, 1)
+
     import gt4py_b200 as gb
     from gt4py_b200 import _lib, stencils, storage
 
     if gb.device_count() <= local:
         raise SystemExit("bench.py: no CUDA device for this rank; the b200 path has no CPU fallback")
     _lib.set_device(local)
+    affinity = bind_near_gpu(local) if world > 1 else None
 
     dist = None
     if world > 1:
@@ -361,6 +414,7 @@ def run_b200(args):
 
     kernels = {"hdiff": roof("hdiff", t_h, "hdiff_tma_kernel"), "vadv": roof("vadv", t_v, "vadv_fused2_kernel")}
     dominant = "vadv" if t_v >= t_h else "hdiff"
+    halo_line = halo_leg(halo, args.sets, stream, gb, barrier, allmax) if halo is not None else None
 
     # ---- e2e: host buffers in, host buffers out, every step (public API) ----------------------------
     e2e = None
@@ -393,7 +447,10 @@ def run_b200(args):
             "e2e": e2e, "cpu_baseline": cpu, "clocks": clocks,
             "gpu_launches": 2 * args.steps + (2 * halo.launches_per_refresh * args.steps if halo else 0),
         }
-        print(json.dumps(line), flush=True)
+        if halo_line is not None:
+            line["halo_exchange"] = halo_line
+            line["config"]["host_affinity"] = affinity
+        os.write(result_fd, (json.dumps(line) + "\n").encode())
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()

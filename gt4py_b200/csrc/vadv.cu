@@ -192,13 +192,13 @@ extern "C" int b200_vadv(const b200_field *utens_stage, const b200_field *u_stag
         B200_CUDA_CHECK(cudaGetDevice(&dev));
         B200_CUDA_CHECK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
     }
-    if (variant == 0 || variant == 10) {  // tuned fused-sweep kernel (vadv_fused.cu)
-        bool handled = false;
-        if ((rc = launch_vadv_fused(a, stream, &handled))) return rc;
+    if (variant == 0 || variant == 10 || variant == 11) {  // tuned fused-sweep kernel (vadv_fused.cu)
+        bool handled = false;  // variant 10: 2 levels per ring stage, 11: 4 levels per stage
+        if ((rc = launch_vadv_fused(a, variant == 11 ? 4 : 2, stream, &handled))) return rc;
         if (handled) return B200_OK;
         if (variant != 0) {
-            set_error("vadv variant 10 needs unit I stride, 16-byte aligned origins, even J/K strides and nk "
-                      "small enough for the on-chip LIFO");
+            set_error("vadv variant %d needs unit I stride, 16-byte aligned origins, even J/K strides and nk "
+                      "small enough for the on-chip LIFO", variant);
             return B200_EUNSUP;
         }
     }

@@ -201,7 +201,7 @@ __device__ __forceinline__ void rec_level2_exact(const Pre2 &p, double &ccol, do
 // host launchers (vadv_tma.cu)
 int launch_vadv_tma(const VadvArgs &a, int variant, cudaStream_t stream, bool *handled);
 // (vadv_fused.cu)
-int launch_vadv_fused(const VadvArgs &a, cudaStream_t stream, bool *handled);
+int launch_vadv_fused(const VadvArgs &a, int levels_per_stage, cudaStream_t stream, bool *handled);
 // (vadv_tmem.cu)
 int launch_vadv_tmem(const VadvArgs &a, int variant, cudaStream_t stream, bool *handled);
 

@@ -21,11 +21,12 @@ namespace b200 {
 
 namespace {
 
-constexpr int FK = 2;  // levels per stage
-
-template <int TI>
+// FK = levels per stage (2 or 4): one tcgen05.st / tcgen05.ld (.x8 / .x16) moves the LIFO entries of a stage.
+template <int TI, int FK>
 struct Fused {
     using G = VmGeom<TI, FK>;
+    static constexpr uint32_t TCOLS = 4u * FK;  // 32-bit TMEM columns per LIFO slot
+    static constexpr int LIFO_SLOT = 2 * FK * VM_COLS;  // doubles per shared-memory LIFO slot
 
     // per-thread state of the consumer warps
     struct Ctx {
@@ -50,16 +51,15 @@ struct Fused {
         bool valid_old;
     };
 
-    __device__ static __forceinline__ void push(Ctx &c, int q, double c0, double d0, double c1, double d1)
+    // v = (ccol, dcol) of the FK levels of a stage, lowest level first
+    __device__ static __forceinline__ void push(Ctx &c, int q, const double (&v)[2 * FK])
     {
         if (q < c.nTs) {
-            tmem_push2(c.tstack + 8u * (uint32_t)q, c0, d0, c1, d1);
+            tmem_push_n<FK>(c.tstack + TCOLS * (uint32_t)q, v);
         } else {
-            double *s = c.lifo_t + (size_t)(q - c.nTs) * 4 * VM_COLS;
-            s[0] = c0;
-            s[VM_COLS] = d0;
-            s[2 * VM_COLS] = c1;
-            s[3 * VM_COLS] = d1;
+            double *s = c.lifo_t + (size_t)(q - c.nTs) * LIFO_SLOT;
+#pragma unroll
+            for (int u = 0; u < 2 * FK; ++u) s[u * VM_COLS] = v[u];
         }
     }
 
@@ -67,46 +67,48 @@ struct Fused {
     __device__ static __forceinline__ void solve_push(Ctx &c, int q)
     {
         double cc = c.ccol, dc = c.dcol;
+        double v[2 * FK];
         bool ok = true;
-        rec_level2(c.pend[0], cc, dc, ok);
-        const double c0 = cc, d0 = dc;
-        rec_level2(c.pend[1], cc, dc, ok);
-        if (ok) {
-            c.ccol = cc;
-            c.dcol = dc;
-            push(c, q, c0, d0, cc, dc);
-        } else {  // a divisor outside 2^-999 .. 2^999 (or not finite): IEEE division, same rounding
-            double c0e = c.ccol, d0e = c.dcol;
-            rec_level2_exact(c.pend[0], c0e, d0e);
-            double c1e = c0e, d1e = d0e;
-            rec_level2_exact(c.pend[1], c1e, d1e);
-            c.ccol = c1e;
-            c.dcol = d1e;
-            push(c, q, c0e, d0e, c1e, d1e);
+#pragma unroll
+        for (int u = 0; u < FK; ++u) {
+            rec_level2(c.pend[u], cc, dc, ok);
+            v[2 * u] = cc;
+            v[2 * u + 1] = dc;
         }
+        if (!ok) {  // a divisor outside 2^-999 .. 2^999 (or not finite): IEEE division, same rounding
+            cc = c.ccol;
+            dc = c.dcol;
+#pragma unroll
+            for (int u = 0; u < FK; ++u) {
+                rec_level2_exact(c.pend[u], cc, dc);
+                v[2 * u] = cc;
+                v[2 * u + 1] = dc;
+            }
+        }
+        c.ccol = cc;
+        c.dcol = dc;
+        push(c, q, v);
     }
 
     template <bool FWD, bool BWD>
     __device__ static __forceinline__ void sweep(Ctx &c, const int dir)
     {
         const int t = c.t;
-        const bool pad_top = (c.nk & 1) != 0;  // level 2*nstages-1 does not exist
+        const int ntop = c.nk - (c.nstages - 1) * FK;  // levels that exist in the top stage (1 .. FK)
         int qprev = 0;
 #pragma unroll 1
         for (int ks = 0; ks < c.nstages; ++ks) {
             const int q = dir ? c.nstages - 1 - ks : ks;  // LIFO slot popped now, refilled next iteration
             const bool tm = q < c.nTs;
-            Raw8 raw;
-            double cc0, dc0, cc1, dc1;
+            RawN<FK> raw;
+            double v[2 * FK];  // (ccol, dcol) of the popped stage
             if (BWD) {
                 if (tm) {
-                    tmem_pop2_issue(c.tstack + 8u * (uint32_t)q, raw);
+                    tmem_pop_n_issue<FK>(c.tstack + TCOLS * (uint32_t)q, raw);
                 } else {
-                    const double *s = c.lifo_t + (size_t)(q - c.nTs) * 4 * VM_COLS;
-                    cc0 = s[0];
-                    dc0 = s[VM_COLS];
-                    cc1 = s[2 * VM_COLS];
-                    dc1 = s[3 * VM_COLS];
+                    const double *s = c.lifo_t + (size_t)(q - c.nTs) * LIFO_SLOT;
+#pragma unroll
+                    for (int u = 0; u < 2 * FK; ++u) v[u] = s[u * VM_COLS];
                 }
             }
             if (FWD) {
@@ -133,25 +135,27 @@ struct Fused {
             if (BWD) {
                 mbar_wait(&c.fullB[c.sB], c.phB);
                 const double *slot = reinterpret_cast<const double *>(c.ringB + (size_t)c.sB * G::SLOT_B) + t;
-                const double up0 = slot[0], up1 = slot[VM_COLS];
+                double up[FK];
+#pragma unroll
+                for (int u = 0; u < FK; ++u) up[u] = slot[u * VM_COLS];
                 __syncwarp();
                 if (c.lane == 0) mbar_arrive(&c.emptyB[c.sB]);
                 if (++c.sB == c.SB) { c.sB = 0; c.phB ^= 1; }
                 if (tm) {
-                    tmem_pop2_wait(raw);
-                    cc0 = __hiloint2double((int)raw.r[1], (int)raw.r[0]);
-                    dc0 = __hiloint2double((int)raw.r[3], (int)raw.r[2]);
-                    cc1 = __hiloint2double((int)raw.r[5], (int)raw.r[4]);
-                    dc1 = __hiloint2double((int)raw.r[7], (int)raw.r[6]);
+                    tmem_pop_n_wait<FK>(raw);
+#pragma unroll
+                    for (int u = 0; u < 2 * FK; ++u)
+                        v[u] = __hiloint2double((int)raw.r[2 * u + 1], (int)raw.r[2 * u]);
                 }
-                // levels 2*kb+1 then 2*kb of the old tile (kb = nstages-1-ks)  :305-312
-                if (!(ks == 0 && pad_top)) {
-                    c.datacol = dc1 - cc1 * c.datacol;
-                    if (c.valid_old) __stcs(c.op + c.sk, c.dtr * (c.datacol - up1));
+                // levels FK*kb + FK-1 down to FK*kb of the old tile (kb = nstages-1-ks)  :305-312
+#pragma unroll
+                for (int u = FK - 1; u >= 0; --u) {
+                    if (u == 0 || ks > 0 || u < ntop) {  // the top stage may be partly beyond nk
+                        c.datacol = v[2 * u + 1] - v[2 * u] * c.datacol;
+                        if (c.valid_old) __stcs(c.op + u * c.sk, c.dtr * (c.datacol - up[u]));
+                    }
                 }
-                c.datacol = dc0 - cc0 * c.datacol;
-                if (c.valid_old) __stcs(c.op, c.dtr * (c.datacol - up0));
-                c.op -= 2 * c.sk;
+                c.op -= FK * c.sk;
             }
             qprev = q;
         }
@@ -161,13 +165,14 @@ struct Fused {
 
 }  // namespace
 
-template <int TI>
+template <int TI, int FK>
 __global__ void __launch_bounds__(VM_THREADS, 1)
 vadv_fused2_kernel(VadvArgs a, const __grid_constant__ CUtensorMap m_us, const __grid_constant__ CUtensorMap m_w,
                    const __grid_constant__ CUtensorMap m_up, const __grid_constant__ CUtensorMap m_ut,
-                   const __grid_constant__ CUtensorMap m_uts, int S, int SB, int nTs, int tiles_i, int ntiles)
+                   const __grid_constant__ CUtensorMap m_uts, int S, int SB, int nTs, int tiles_i, int ntiles,
+                   uint64_t pol_stream, uint64_t pol_keep, uint64_t pol_bwd)
 {
-    using F = Fused<TI>;
+    using F = Fused<TI, FK>;
     using G = typename F::G;
     extern __shared__ __align__(1024) unsigned char smem[];
     uint64_t *fullF = reinterpret_cast<uint64_t *>(smem);
@@ -217,11 +222,11 @@ vadv_fused2_kernel(VadvArgs a, const __grid_constant__ CUtensorMap m_us, const _
                     mbar_expect_tx(&fullF[sF], G::TX_F);
                     unsigned char *slot = ringF + (size_t)sF * G::SLOT_F;
                     const int k0 = ks * FK;
-                    tma_load_3d(slot, &m_us, ci, cj, k0 + 1, &fullF[sF], L2_EVICT_FIRST);
-                    tma_load_3d(slot + G::F_BYTES, &m_up, ci, cj, k0, &fullF[sF], L2_EVICT_LAST);
-                    tma_load_3d(slot + 2 * G::F_BYTES, &m_ut, ci, cj, k0, &fullF[sF], L2_EVICT_FIRST);
-                    tma_load_3d(slot + 3 * G::F_BYTES, &m_uts, ci, cj, k0, &fullF[sF], L2_EVICT_FIRST);
-                    tma_load_3d(slot + 4 * G::F_BYTES, &m_w, ci, cj, k0 + 1, &fullF[sF], L2_EVICT_FIRST);
+                    tma_load_3d(slot, &m_us, ci, cj, k0 + 1, &fullF[sF], pol_stream);
+                    tma_load_3d(slot + G::F_BYTES, &m_up, ci, cj, k0, &fullF[sF], pol_keep);
+                    tma_load_3d(slot + 2 * G::F_BYTES, &m_ut, ci, cj, k0, &fullF[sF], pol_stream);
+                    tma_load_3d(slot + 3 * G::F_BYTES, &m_uts, ci, cj, k0, &fullF[sF], pol_stream);
+                    tma_load_3d(slot + 4 * G::F_BYTES, &m_w, ci, cj, k0 + 1, &fullF[sF], pol_stream);
                     if (++sF == S) { sF = 0; phF ^= 1; }
                 }
             }
@@ -237,7 +242,7 @@ vadv_fused2_kernel(VadvArgs a, const __grid_constant__ CUtensorMap m_us, const _
                 for (int ks = nstages - 1; ks >= 0; --ks) {
                     mbar_wait(&emptyB[sB], phB ^ 1);
                     mbar_expect_tx(&fullB[sB], G::TX_B);
-                    tma_load_3d(ringB + (size_t)sB * G::SLOT_B, &m_up, ci, cj, ks * FK, &fullB[sB], L2_EVICT_FIRST);
+                    tma_load_3d(ringB + (size_t)sB * G::SLOT_B, &m_up, ci, cj, ks * FK, &fullB[sB], pol_bwd);
                     if (++sB == SB) { sB = 0; phB ^= 1; }
                 }
             }
@@ -310,7 +315,7 @@ vadv_fused2_kernel(VadvArgs a, const __grid_constant__ CUtensorMap m_us, const _
     if (warp == VM_CWARPS) tmem_dealloc(tmem_base, VM_TMEM_COLS);
 }
 
-template <int TI>
+template <int TI, int FK>
 static int launch_fused2(const VadvArgs &a, cudaStream_t stream, bool *handled)
 {
     using G = VmGeom<TI, FK>;
@@ -321,19 +326,19 @@ static int launch_fused2(const VadvArgs &a, cudaStream_t stream, bool *handled)
         B200_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
         B200_CUDA_CHECK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
     }
-    static const int env_s = env_int("B200_VADV_STAGES", 0);
-    static const int env_sb = env_int("B200_VADV_BSTAGES", 0);
+    const int env_s = env_int("B200_VADV_STAGES", 0);   // tuning hooks, read at every launch
+    const int env_sb = env_int("B200_VADV_BSTAGES", 0);
     const int nstages = (a.nk + FK - 1) / FK;
-    const int tmem_slots = VM_TMEM_LEVELS / FK;  // 32 stage slots of 8 columns per thread
+    const int tmem_slots = VM_TMEM_LEVELS / FK;  // stage slots of 4 * FK columns per thread
     const int nTs = nstages < tmem_slots ? nstages : tmem_slots;
     const size_t lifo = (size_t)(nstages - nTs) * 2 * FK * VM_COLS * 8;
-    int SB = env_sb > 0 ? env_sb : 6;
+    int SB = env_sb > 0 ? env_sb : (FK == 2 ? 6 : 3);
     if (SB > VM_MAX_STAGES) SB = VM_MAX_STAGES;
     long avail = (long)max_smem - VM_BAR_BYTES - (long)lifo;
     while (SB > 2 && (long)SB * G::SLOT_B > avail / 4) --SB;
     avail -= (long)SB * G::SLOT_B;
     int S = avail > 0 ? (int)(avail / G::SLOT_F) : 0;
-    const int want = env_s > 0 ? env_s : 5;
+    const int want = env_s > 0 ? env_s : (FK == 2 ? 5 : 3);
     if (S > want) S = want;
     if (S > VM_MAX_STAGES) S = VM_MAX_STAGES;
     if (S < 2) return B200_OK;  // LIFO does not fit on chip: not handled here
@@ -352,9 +357,16 @@ static int launch_fused2(const VadvArgs &a, cudaStream_t stream, bool *handled)
     const int tiles_i = (a.ni + TI - 1) / TI, tiles_j = (a.nj + G::TJ - 1) / G::TJ;
     const int ntiles = tiles_i * tiles_j;
     const int grid = ntiles < sms ? ntiles : sms;
-    auto kern = vadv_fused2_kernel<TI>;
+    auto kern = vadv_fused2_kernel<TI, FK>;
     B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<grid, VM_THREADS, smem, stream>>>(a, m_us, m_w, m_up, m_ut, m_uts, S, SB, nTs, tiles_i, ntiles);
+    // L2 policies of the streaming loads, the forward u_pos load (re-read by the BACKWARD sweep one tile later)
+    // and that re-read; tuning hooks: 0 = normal, 1 = evict_first, 2 = evict_last
+    static const uint64_t pols[3] = {L2_EVICT_NORMAL, L2_EVICT_FIRST, L2_EVICT_LAST};
+    const uint64_t pol_stream = pols[env_int("B200_VADV_POL_STREAM", 1) % 3];
+    const uint64_t pol_keep = pols[env_int("B200_VADV_POL_KEEP", 2) % 3];
+    const uint64_t pol_bwd = pols[env_int("B200_VADV_POL_BWD", 1) % 3];
+    kern<<<grid, VM_THREADS, smem, stream>>>(a, m_us, m_w, m_up, m_ut, m_uts, S, SB, nTs, tiles_i, ntiles, pol_stream,
+                                             pol_keep, pol_bwd);
     B200_CUDA_CHECK(cudaGetLastError());
     *handled = true;
     return B200_OK;
@@ -362,7 +374,7 @@ static int launch_fused2(const VadvArgs &a, cudaStream_t stream, bool *handled)
 
 // Launch the tuned fused kernel if the layout allows it (same preconditions as vadv_tma.cu); *handled =
 // false with B200_OK means "use another variant".
-int launch_vadv_fused(const VadvArgs &a, cudaStream_t stream, bool *handled)
+int launch_vadv_fused(const VadvArgs &a, int levels_per_stage, cudaStream_t stream, bool *handled)
 {
     *handled = false;
     if (!tma_compatible(a.u_stage.p, a.u_stage.si, a.u_stage.sj, a.u_stage.sk) ||
@@ -371,9 +383,13 @@ int launch_vadv_fused(const VadvArgs &a, cudaStream_t stream, bool *handled)
         !tma_compatible(a.utens.p, a.utens.si, a.utens.sj, a.utens.sk) ||
         !tma_compatible(a.utens_stage.p, a.utens_stage.si, a.utens_stage.sj, a.utens_stage.sk))
         return B200_OK;
-    return a.ni > 64 ? launch_fused2<128>(a, stream, handled)
-         : a.ni > 32 ? launch_fused2<64>(a, stream, handled)
-                     : launch_fused2<32>(a, stream, handled);
+    if (levels_per_stage == 4)
+        return a.ni > 64 ? launch_fused2<128, 4>(a, stream, handled)
+             : a.ni > 32 ? launch_fused2<64, 4>(a, stream, handled)
+                         : launch_fused2<32, 4>(a, stream, handled);
+    return a.ni > 64 ? launch_fused2<128, 2>(a, stream, handled)
+         : a.ni > 32 ? launch_fused2<64, 2>(a, stream, handled)
+                     : launch_fused2<32, 2>(a, stream, handled);
 }
 
 }  // namespace b200

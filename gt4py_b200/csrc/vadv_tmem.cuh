@@ -109,4 +109,61 @@ __device__ __forceinline__ void tmem_pop2_wait(Raw8 &v)
                    "+r"(v.r[7])::"memory");
 }
 
+// Generic forms over L levels per LIFO slot (L = 2: .x8, L = 4: .x16); v = (ccol, dcol) per level.
+template <int L>
+struct RawN {
+    uint32_t r[4 * L];
+};
+template <int L>
+__device__ __forceinline__ void tmem_push_n(uint32_t taddr, const double (&v)[2 * L])
+{
+    static_assert(L == 2 || L == 4, "levels per stage must be 2 or 4");
+    if constexpr (L == 2) {
+        tmem_push2(taddr, v[0], v[1], v[2], v[3]);
+    } else {
+        asm volatile(
+            "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, "
+            "%14, %15, %16};" ::"r"(taddr),
+            "r"(__double2loint(v[0])), "r"(__double2hiint(v[0])), "r"(__double2loint(v[1])), "r"(__double2hiint(v[1])),
+            "r"(__double2loint(v[2])), "r"(__double2hiint(v[2])), "r"(__double2loint(v[3])), "r"(__double2hiint(v[3])),
+            "r"(__double2loint(v[4])), "r"(__double2hiint(v[4])), "r"(__double2loint(v[5])), "r"(__double2hiint(v[5])),
+            "r"(__double2loint(v[6])), "r"(__double2hiint(v[6])), "r"(__double2loint(v[7])), "r"(__double2hiint(v[7]))
+            : "memory");
+    }
+}
+template <int L>
+__device__ __forceinline__ void tmem_pop_n_issue(uint32_t taddr, RawN<L> &v)
+{
+    if constexpr (L == 2) {
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                     : "=r"(v.r[0]), "=r"(v.r[1]), "=r"(v.r[2]), "=r"(v.r[3]), "=r"(v.r[4]), "=r"(v.r[5]),
+                       "=r"(v.r[6]), "=r"(v.r[7])
+                     : "r"(taddr)
+                     : "memory");
+    } else {
+        asm volatile(
+            "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, "
+            "%15}, [%16];"
+            : "=r"(v.r[0]), "=r"(v.r[1]), "=r"(v.r[2]), "=r"(v.r[3]), "=r"(v.r[4]), "=r"(v.r[5]), "=r"(v.r[6]),
+              "=r"(v.r[7]), "=r"(v.r[8]), "=r"(v.r[9]), "=r"(v.r[10]), "=r"(v.r[11]), "=r"(v.r[12]), "=r"(v.r[13]),
+              "=r"(v.r[14]), "=r"(v.r[15])
+            : "r"(taddr)
+            : "memory");
+    }
+}
+template <int L>
+__device__ __forceinline__ void tmem_pop_n_wait(RawN<L> &v)
+{
+    if constexpr (L == 2) {
+        asm volatile("tcgen05.wait::ld.sync.aligned;"
+                     : "+r"(v.r[0]), "+r"(v.r[1]), "+r"(v.r[2]), "+r"(v.r[3]), "+r"(v.r[4]), "+r"(v.r[5]),
+                       "+r"(v.r[6]), "+r"(v.r[7])::"memory");
+    } else {
+        asm volatile("tcgen05.wait::ld.sync.aligned;"
+                     : "+r"(v.r[0]), "+r"(v.r[1]), "+r"(v.r[2]), "+r"(v.r[3]), "+r"(v.r[4]), "+r"(v.r[5]),
+                       "+r"(v.r[6]), "+r"(v.r[7]), "+r"(v.r[8]), "+r"(v.r[9]), "+r"(v.r[10]), "+r"(v.r[11]),
+                       "+r"(v.r[12]), "+r"(v.r[13]), "+r"(v.r[14]), "+r"(v.r[15])::"memory");
+    }
+}
+
 }  // namespace b200

@@ -313,6 +313,13 @@ class HaloExchanger:
         L.synchronize()
         self._finalized = True
 
+    def bytes_received(self, group: int) -> int:
+        """Bytes this rank's halo cells of `group` receive from its neighbours per refresh."""
+        total = 0
+        for f, b, _ in self._boxes_of(self.decomp.rank, self._groups[group]):
+            total += int(b.extent[0]) * int(b.extent[1]) * int(b.extent[2]) * self._groups[group][f][0].dtype.itemsize
+        return total
+
     # -- per-step operations ---------------------------------------------------------------------------
     def _launch(self, table, mode, stream):
         dev, n, blocks = table
