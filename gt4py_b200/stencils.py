@@ -63,6 +63,20 @@ class HorizontalDiffusion(_LibraryStencil):
                                          self._variant_, _lib.stream_handle(stream)))
 
 
+class HorizontalDiffusionFloat32(HorizontalDiffusion):
+    """The same definition built with float32 fields and ``literal_float_precision=32`` (every literal and
+    temporary float32): csrc/hdiff.cu with T = float, variants 1-3."""
+
+    _gt_field_info_ = {
+        "in_field": FieldInfo(access=AccessKind.READ, boundary=Boundary(((2, 2), (2, 2), (0, 0))), axes=_IJK,
+                              data_dims=(), dtype=np.dtype("float32")),
+        "out_field": FieldInfo(access=AccessKind.WRITE, boundary=_B0, axes=_IJK, data_dims=(),
+                               dtype=np.dtype("float32")),
+        "coeff": FieldInfo(access=AccessKind.READ, boundary=_B0, axes=_IJK, data_dims=(), dtype=np.dtype("float32")),
+    }
+    _gt_options_ = {"name": "horizontal_diffusion_float32", "module": __name__}
+
+
 class SimpleHorizontalDiffusion(HorizontalDiffusion):
     """simple_horizontal_diffusion(in_field, coeff, out_field) -- stencil_definitions.py:206-216."""
 

@@ -124,9 +124,11 @@ B200_API int b200_graph_destroy(void *graph_exec);
 /* horizontal_diffusion(in_field, out_field, coeff): reference definition
  * tests/cartesian_tests/integration_tests/multi_feature_tests/stencil_definitions.py:316-328.
  * `limiter` = 1 for that stencil, 0 for simple_horizontal_diffusion (:206-216).
- * in_field needs a halo of 2 in I and J around `domain`. float64.
- * variants: 1 point kernel, 2/3 register J-march (prefetch depth 2/4), 4 alternating march directions,
- * 5 TMA-fed shared-memory rings (the `auto` choice when strides/alignment allow). */
+ * in_field needs a halo of 2 in I and J around `domain`.  All three fields float64, or all three float32
+ * (the definition built with float32 fields and `literal_float_precision=32`: float32 literals and temporaries).
+ * variants: 1 point kernel, 2/3 register J-march (prefetch depth 2/4), 4 alternating march directions (float64),
+ * 5 TMA-fed shared-memory rings (float64; the `auto` choice when strides/alignment allow and the fields exceed
+ * the L2). */
 B200_API int b200_hdiff(const b200_field *in_field, const b200_field *out_field, const b200_field *coeff,
                const int64_t domain[3], int limiter, int variant, void *stream);
 

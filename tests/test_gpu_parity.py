@@ -132,6 +132,32 @@ def test_vadv_vs_oracle(dom, variant):
     assert np.array_equal(out, ref)
 
 
+@pytest.mark.parametrize("variant", [0, 1, 2, 3])
+@pytest.mark.parametrize("dom", [(128, 128, 8), (61, 59, 5), (60, 8, 1), (121, 33, 2), (2, 2, 2), (300, 7, 3)])
+def test_hdiff_float32_vs_oracle(dom, variant):
+    """The pure-float32 build (float32 fields and literals) on the library kernel with T = float: bit-exact
+    against the numpy float32 restatement that the reference's own output pins (tests/test_oracle.py)."""
+    from oracle.hdiff_f32 import hdiff_f32
+
+    f = {k: v.astype(np.float32) for k, v in gen.hdiff_inputs(*dom, seed=321).items()}
+    ref = hdiff_f32(f["in_field"], f["out_field"].copy(), f["coeff"], domain=dom)
+    d = {k: _dev(v, (2, 2, 0)) for k, v in f.items()}
+    st = stencils.HorizontalDiffusionFloat32.with_variant(variant)
+    st(d["in_field"], d["out_field"], d["coeff"], origin=(2, 2, 0), domain=dom)
+    out = d["out_field"].asnumpy()
+    assert out.dtype == np.float32 and np.array_equal(out, ref)
+
+
+def test_hdiff_float32_rejects_float64_only_variants():
+    dom = (32, 8, 2)
+    f = {k: v.astype(np.float32) for k, v in gen.hdiff_inputs(*dom, seed=1).items()}
+    d = {k: _dev(v, (2, 2, 0)) for k, v in f.items()}
+    with pytest.raises(gb.B200Error) as exc:
+        stencils.HorizontalDiffusionFloat32.with_variant(5)(d["in_field"], d["out_field"], d["coeff"],
+                                                            origin=(2, 2, 0), domain=dom)
+    assert exc.value.code == -3
+
+
 def test_hdiff_subdomain_and_offset_origin():
     """origin/domain select a sub-box: points outside it must be untouched."""
     f = gen.hdiff_inputs(40, 30, 4, seed=5)

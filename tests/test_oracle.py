@@ -86,3 +86,21 @@ def test_strided_layout_matches_c_order():
     fi = {k: np.asfortranarray(v) for k, v in f.items()}
     out = oracle.hdiff(fi["in_field"], fi["out_field"], fi["coeff"], domain=(13, 9, 4))
     assert np.array_equal(out, ref)
+
+
+def test_hdiff_f32_oracle_is_pinned_by_the_reference():
+    """oracle/hdiff_f32.py (numpy float32 restatement) against the golden outputs the reference's numpy backend
+    produced for horizontal_diffusion built with float32 fields and literal_float_precision=32."""
+    import json
+
+    from oracle.hdiff_f32 import hdiff_f32
+
+    d = os.path.join(os.path.dirname(__file__), "golden", "generated", "horizontal_diffusion__f32lit")
+    g = np.load(os.path.join(d, "golden.npz"))
+    with open(os.path.join(d, "case.json")) as fh:
+        case = json.load(fh)
+    out = g["in__out_field"].copy()
+    hdiff_f32(g["in__in_field"], out, g["in__coeff"], domain=tuple(case["domain"]),
+              origin=tuple(case["origins"]["in_field"]), out_origin=tuple(case["origins"]["out_field"]),
+              coeff_origin=tuple(case["origins"]["coeff"]))
+    assert out.dtype == np.float32 and np.array_equal(out, g["out__out_field"])

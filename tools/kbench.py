@@ -20,10 +20,10 @@ from oracle import inputs as gen  # noqa: E402
 ALG_BYTES = {"hdiff": 24, "vadv": 48, "tridiag": 56}
 
 
-def make_sets(stencil, ni, nj, nk, nsets):
+def make_sets(stencil, ni, nj, nk, nsets, dtype="float64"):
     sets = []
     if stencil == "hdiff":
-        f = gen.hdiff_inputs(ni, nj, nk)
+        f = {k: v.astype(dtype) for k, v in gen.hdiff_inputs(ni, nj, nk).items()}
         for _ in range(nsets):
             sets.append({k: storage.from_array(v, backend="b200", aligned_index=(2, 2, 0)) for k, v in f.items()})
     elif stencil == "vadv":
@@ -55,6 +55,8 @@ def main():
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--sets", type=int, default=3)
+    ap.add_argument("--dtype", default="float64", choices=["float64", "float32"],
+                    help="float32: hdiff only (the pure-float32 build; 12 B/point algorithmic)")
     ap.add_argument("--sweep", default="", help="environment sweep, e.g. 'B200_HDIFF_NW=2,3;B200_HDIFF_NS=3,4' "
                     "(cartesian product; the launchers read these hooks at every call)")
     ap.add_argument("--check", type=int, default=-1, help="compare each run's output of set 0 bit-for-bit with "
@@ -64,7 +66,11 @@ def main():
     dom = (ni, nj, nk)
     cls = {"hdiff": stencils.HorizontalDiffusion, "vadv": stencils.VerticalAdvectionDycore,
            "tridiag": stencils.TridiagonalSolver}[a.stencil]
-    sets = make_sets(a.stencil, ni, nj, nk, a.sets)
+    if a.dtype == "float32":
+        assert a.stencil == "hdiff", "float32 library kernel: hdiff only"
+        cls = stencils.HorizontalDiffusionFloat32
+    alg_bytes = ALG_BYTES[a.stencil] // (2 if a.dtype == "float32" else 1)
+    sets = make_sets(a.stencil, ni, nj, nk, a.sets, a.dtype)
     n = ni * nj * nk
     import itertools
 
@@ -96,8 +102,8 @@ def main():
             extra["bit_exact"] = bool(np.array_equal(sets[0]["out_field"].asnumpy(), ref_out))
         print(json.dumps({"stencil": a.stencil, "shape": dom, "variant": v, **extra, "ms_min": round(best, 4),
                           "ms_median": round(med, 4), "gpts_s_median": round(n / med / 1e6, 2),
-                          "alg_GBs_median": round(n * ALG_BYTES[a.stencil] / med / 1e6, 1),
-                          "alg_GBs_best": round(n * ALG_BYTES[a.stencil] / best / 1e6, 1)}), flush=True)
+                          "alg_GBs_median": round(n * alg_bytes / med / 1e6, 1),
+                          "alg_GBs_best": round(n * alg_bytes / best / 1e6, 1), "dtype": a.dtype}), flush=True)
 
 
 if __name__ == "__main__":

@@ -94,6 +94,9 @@ def definitions():
         dtypes = {a: gtscript.Field[np.float32] for a in spec.args}
         dtypes.update({a: np.float32 for a in spec.kwonlyargs})
         defs[name + "__f32"] = (annotate_function(fn, dtypes), ext)
+        # pure float32: float32 fields AND float32 literals (`literal_float_precision=32`, gtscript.py:242-290,
+        # ADR docs/development/ADRs/cartesian/frontend/literal-precision.md) -- SURVEY.md 8(f) rank 4
+        defs[name + "__f32lit"] = (annotate_function(fn, dtypes), ext, {}, {"literal_float_precision": 32})
     return defs
 
 
@@ -107,11 +110,13 @@ def main():
     report_path = os.path.join(OUT, "REPORT.json")
     report = json.load(open(report_path)) if sys.argv[1:] and os.path.exists(report_path) else {}
     for name in names:
-        fn, ext, *opts = defs[name]
-        opts = opts[0] if opts else {}
+        fn, ext, *rest = defs[name]
+        opts = rest[0] if rest else {}             # b200 backend options
+        common = rest[1] if len(rest) > 1 else {}  # frontend options, given to both builds
         try:
-            ref = gtscript.stencil("numpy", fn, externals=ext, format_source=False, rebuild=True, name=name)
-            b2 = gtscript.stencil("b200", fn, externals=ext, format_source=False, rebuild=True, name=name, **opts)
+            ref = gtscript.stencil("numpy", fn, externals=ext, format_source=False, rebuild=True, name=name, **common)
+            b2 = gtscript.stencil("b200", fn, externals=ext, format_source=False, rebuild=True, name=name, **common,
+                                  **opts)
         except Exception as exc:  # unsupported feature: recorded, not hidden
             report[name] = f"{type(exc).__name__}: {str(exc)[:200]}"
             print("SKIP", name, report[name])

@@ -25,6 +25,9 @@ LIBRARY = {
 }
 
 
+FLOAT32_KERNELS = {"hdiff"}  # library kernels that also exist for all-float32 fields (csrc/hdiff.cu)
+
+
 def main():
     from cartesian_tests.integration_tests.multi_feature_tests import stencil_definitions as sd
     from gt4py.cartesian.backend import from_name
@@ -34,16 +37,33 @@ def main():
 
     from gt4py_b200 import lowering
 
+    import inspect
+
+    import numpy as np
+    from gt4py.cartesian import gtscript
+    from gt4py.cartesian.testing.utils import annotate_function
+
     table = {}
     for name, (kernel, extra, roles, min_k) in LIBRARY.items():
-        builder = StencilBuilder(sd.REGISTRY[name], backend=from_name("numpy"),
-                                 options=BuildOptions(name=name, module="m", format_source=False, rebuild=True)
-                                 ).with_externals(sd.EXTERNALS_REGISTRY[name])
-        plan, _ = lowering.lower(GTIRToOIR().visit(builder.gtir), name, fuse=False)
-        fp = plan["fingerprint"]
-        assert fp["api_order"] == roles, (name, fp["api_order"])
-        table[fp["digest"]] = {"kernel": kernel, **extra, "roles": roles, "min_k": min_k, "reference": name}
-        print(name, fp["digest"])
+        variants = [("float64", sd.REGISTRY[name], {})]
+        if kernel in FLOAT32_KERNELS:
+            # the pure-float32 build: float32 fields and parameters, `literal_float_precision=32`
+            spec = inspect.getfullargspec(sd.REGISTRY[name])
+            dtypes = {a: gtscript.Field[np.float32] for a in spec.args}
+            dtypes.update({a: np.float32 for a in spec.kwonlyargs})
+            variants.append(("float32", annotate_function(sd.REGISTRY[name], dtypes), {"literal_float_precision": 32}))
+        for dtype, fn, opts in variants:
+            builder = StencilBuilder(fn, backend=from_name("numpy"),
+                                     options=BuildOptions(name=name, module="m", format_source=False, rebuild=True,
+                                                          **opts)
+                                     ).with_externals(sd.EXTERNALS_REGISTRY[name])
+            plan, _ = lowering.lower(GTIRToOIR().visit(builder.gtir), name, fuse=False)
+            fp = plan["fingerprint"]
+            assert fp["api_order"] == roles, (name, fp["api_order"])
+            assert fp["digest"] not in table, (name, dtype)
+            table[fp["digest"]] = {"kernel": kernel, **extra, "roles": roles, "min_k": min_k, "reference": name,
+                                   "dtype": dtype}
+            print(name, dtype, fp["digest"])
     out = os.path.join(ROOT, "gt4py_b200", "library_kernels.json")
     with open(out, "w") as fh:
         json.dump({"comment": "made by tools/make_library_fingerprints.py", "kernels": table}, fh, indent=1, sort_keys=True)
