@@ -22,7 +22,10 @@ namespace b200 {
 namespace {
 
 // FK = levels per stage (2 or 4): one tcgen05.st / tcgen05.ld (.x8 / .x16) moves the LIFO entries of a stage.
-template <int TI, int FK>
+// SPILL: the LIFO slots beyond the on-chip capacity (Tensor Memory + shared memory: 88 levels with the default rings)
+// live in a per-CTA global scratch area that is small enough (8 KB per slot and CTA) to stay in the L2; the columns of
+// a tile then cost ~16 B/level of L2 traffic for the spilled levels instead of the whole LIFO going to HBM.
+template <int TI, int FK, bool SPILL>
 struct Fused {
     using G = VmGeom<TI, FK>;
     static constexpr uint32_t TCOLS = 4u * FK;  // 32-bit TMEM columns per LIFO slot
@@ -31,12 +34,13 @@ struct Fused {
     // per-thread state of the consumer warps
     struct Ctx {
         // geometry / constants
-        int t, ti, tj, lane, nk, nstages, nTs, S, SB;
+        int t, ti, tj, lane, nk, nstages, nTs, nOn, S, SB;
         double dtr;
         int64_t sk;
         uint64_t *fullF, *emptyF, *fullB, *emptyB;
         const unsigned char *ringF, *ringB;
         double *lifo_t;     // shared-memory part of the LIFO, this thread's column
+        double *spill_t;    // global-scratch part of the LIFO (slots >= nOn), this thread's column
         uint32_t tstack;    // Tensor-Memory part of the LIFO, this thread's lane / column half
         // ring cursors
         int sF, sB;
@@ -56,10 +60,14 @@ struct Fused {
     {
         if (q < c.nTs) {
             tmem_push_n<FK>(c.tstack + TCOLS * (uint32_t)q, v);
-        } else {
+        } else if (!SPILL || q < c.nOn) {
             double *s = c.lifo_t + (size_t)(q - c.nTs) * LIFO_SLOT;
 #pragma unroll
             for (int u = 0; u < 2 * FK; ++u) s[u * VM_COLS] = v[u];
+        } else {
+            double *g = c.spill_t + (size_t)(q - c.nOn) * LIFO_SLOT;
+#pragma unroll
+            for (int u = 0; u < 2 * FK; ++u) __stcg(g + u * VM_COLS, v[u]);
         }
     }
 
@@ -105,10 +113,14 @@ struct Fused {
             if (BWD) {
                 if (tm) {
                     tmem_pop_n_issue<FK>(c.tstack + TCOLS * (uint32_t)q, raw);
-                } else {
+                } else if (!SPILL || q < c.nOn) {
                     const double *s = c.lifo_t + (size_t)(q - c.nTs) * LIFO_SLOT;
 #pragma unroll
                     for (int u = 0; u < 2 * FK; ++u) v[u] = s[u * VM_COLS];
+                } else {  // written by this very thread one tile earlier: L2
+                    const double *g = c.spill_t + (size_t)(q - c.nOn) * LIFO_SLOT;
+#pragma unroll
+                    for (int u = 0; u < 2 * FK; ++u) v[u] = __ldcg(g + u * VM_COLS);
                 }
             }
             if (FWD) {
@@ -165,14 +177,14 @@ struct Fused {
 
 }  // namespace
 
-template <int TI, int FK>
+template <int TI, int FK, bool SPILL>
 __global__ void __launch_bounds__(VM_THREADS, 1)
 vadv_fused2_kernel(VadvArgs a, const __grid_constant__ CUtensorMap m_us, const __grid_constant__ CUtensorMap m_w,
                    const __grid_constant__ CUtensorMap m_up, const __grid_constant__ CUtensorMap m_ut,
                    const __grid_constant__ CUtensorMap m_uts, int S, int SB, int nTs, int tiles_i, int ntiles,
-                   uint64_t pol_stream, uint64_t pol_keep, uint64_t pol_bwd)
+                   uint64_t pol_stream, uint64_t pol_keep, uint64_t pol_bwd, int nOn, double *spill)
 {
-    using F = Fused<TI, FK>;
+    using F = Fused<TI, FK, SPILL>;
     using G = typename F::G;
     extern __shared__ __align__(1024) unsigned char smem[];
     uint64_t *fullF = reinterpret_cast<uint64_t *>(smem);
@@ -258,6 +270,8 @@ vadv_fused2_kernel(VadvArgs a, const __grid_constant__ CUtensorMap m_us, const _
         c.nk = nk;
         c.nstages = nstages;
         c.nTs = nTs;
+        c.nOn = nOn;
+        c.spill_t = SPILL ? spill + (size_t)blockIdx.x * (size_t)(nstages - nOn) * F::LIFO_SLOT + c.t : nullptr;
         c.S = S;
         c.SB = SB;
         c.dtr = a.dtr_stage;
@@ -331,17 +345,31 @@ static int launch_fused2(const VadvArgs &a, cudaStream_t stream, bool *handled)
     const int nstages = (a.nk + FK - 1) / FK;
     const int tmem_slots = VM_TMEM_LEVELS / FK;  // stage slots of 4 * FK columns per thread
     const int nTs = nstages < tmem_slots ? nstages : tmem_slots;
-    const size_t lifo = (size_t)(nstages - nTs) * 2 * FK * VM_COLS * 8;
-    int SB = env_sb > 0 ? env_sb : (FK == 2 ? 6 : 3);
-    if (SB > VM_MAX_STAGES) SB = VM_MAX_STAGES;
+    const size_t slot_bytes = (size_t)2 * FK * VM_COLS * 8;
+    const int want_s = env_s > 0 ? env_s : (FK == 2 ? 5 : 3);
+    const int want_sb = env_sb > 0 ? env_sb : (FK == 2 ? 6 : 3);
+    // 1. whole LIFO on chip, rings shrunk if need be (down to 2 stages)
+    size_t lifo = (size_t)(nstages - nTs) * slot_bytes;
+    int nOn = nstages;
+    int SB = want_sb > VM_MAX_STAGES ? VM_MAX_STAGES : want_sb;
     long avail = (long)max_smem - VM_BAR_BYTES - (long)lifo;
     while (SB > 2 && (long)SB * G::SLOT_B > avail / 4) --SB;
     avail -= (long)SB * G::SLOT_B;
     int S = avail > 0 ? (int)(avail / G::SLOT_F) : 0;
-    const int want = env_s > 0 ? env_s : (FK == 2 ? 5 : 3);
-    if (S > want) S = want;
+    if (S > want_s) S = want_s;
     if (S > VM_MAX_STAGES) S = VM_MAX_STAGES;
-    if (S < 2) return B200_OK;  // LIFO does not fit on chip: not handled here
+    if (S < 2) {
+        // 2. nk too large for that (> ~108): full-depth rings, as many LIFO slots in shared memory as then fit,
+        //    the rest in the per-CTA global scratch (SPILL)
+        S = want_s > VM_MAX_STAGES ? VM_MAX_STAGES : want_s;
+        SB = want_sb > VM_MAX_STAGES ? VM_MAX_STAGES : want_sb;
+        avail = (long)max_smem - VM_BAR_BYTES - (long)S * G::SLOT_F - (long)SB * G::SLOT_B;
+        if (avail < 0) return B200_OK;
+        const int nSs = (int)(avail / (long)slot_bytes);
+        nOn = nTs + nSs;
+        if (nOn >= nstages) nOn = nstages;  // cannot happen: case 1 would have fitted
+        lifo = (size_t)(nOn - nTs) * slot_bytes;
+    }
     const size_t smem = VM_BAR_BYTES + (size_t)S * G::SLOT_F + (size_t)SB * G::SLOT_B + lifo;
 
     CUtensorMap m_us, m_w, m_up, m_ut, m_uts;
@@ -357,16 +385,38 @@ static int launch_fused2(const VadvArgs &a, cudaStream_t stream, bool *handled)
     const int tiles_i = (a.ni + TI - 1) / TI, tiles_j = (a.nj + G::TJ - 1) / G::TJ;
     const int ntiles = tiles_i * tiles_j;
     const int grid = ntiles < sms ? ntiles : sms;
-    auto kern = vadv_fused2_kernel<TI, FK>;
-    B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     // L2 policies of the streaming loads, the forward u_pos load (re-read by the BACKWARD sweep one tile later)
     // and that re-read; tuning hooks: 0 = normal, 1 = evict_first, 2 = evict_last
     static const uint64_t pols[3] = {L2_EVICT_NORMAL, L2_EVICT_FIRST, L2_EVICT_LAST};
     const uint64_t pol_stream = pols[env_int("B200_VADV_POL_STREAM", 1) % 3];
     const uint64_t pol_keep = pols[env_int("B200_VADV_POL_KEEP", 2) % 3];
     const uint64_t pol_bwd = pols[env_int("B200_VADV_POL_BWD", 1) % 3];
-    kern<<<grid, VM_THREADS, smem, stream>>>(a, m_us, m_w, m_up, m_ut, m_uts, S, SB, nTs, tiles_i, ntiles, pol_stream,
-                                             pol_keep, pol_bwd);
+    if (nOn < nstages) {
+        // spill scratch: grown on demand, per process (launches that need it are ordered by the caller's stream;
+        // concurrent spilling launches on different streams are not supported -- same rule as vadv.cu's scratch)
+        static double *scratch = nullptr;
+        static size_t scratch_bytes = 0;
+        const size_t need = (size_t)grid * (size_t)(nstages - nOn) * slot_bytes;
+        if (need > scratch_bytes) {
+            if (scratch) {
+                B200_CUDA_CHECK(cudaDeviceSynchronize());
+                B200_CUDA_CHECK(cudaFree(scratch));
+            }
+            scratch = nullptr;
+            scratch_bytes = 0;
+            B200_CUDA_CHECK(cudaMalloc(&scratch, need));
+            scratch_bytes = need;
+        }
+        auto kern = vadv_fused2_kernel<TI, FK, true>;
+        B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        kern<<<grid, VM_THREADS, smem, stream>>>(a, m_us, m_w, m_up, m_ut, m_uts, S, SB, nTs, tiles_i, ntiles,
+                                                 pol_stream, pol_keep, pol_bwd, nOn, scratch);
+    } else {
+        auto kern = vadv_fused2_kernel<TI, FK, false>;
+        B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        kern<<<grid, VM_THREADS, smem, stream>>>(a, m_us, m_w, m_up, m_ut, m_uts, S, SB, nTs, tiles_i, ntiles,
+                                                 pol_stream, pol_keep, pol_bwd, nOn, nullptr);
+    }
     B200_CUDA_CHECK(cudaGetLastError());
     *handled = true;
     return B200_OK;

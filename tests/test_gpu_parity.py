@@ -123,7 +123,8 @@ def test_hdiff_vs_oracle(dom, variant):
 
 @pytest.mark.parametrize("variant", [0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11])
 @pytest.mark.parametrize("dom", [(256, 256, 80), (33, 5, 3), (31, 7, 80), (64, 3, 17), (1, 1, 4),
-                                 (100, 6, 137), (129, 2, 5), (300, 37, 7), (65, 130, 79), (40, 9, 82), (20, 4, 6)])
+                                 (100, 6, 137), (129, 2, 5), (300, 37, 7), (65, 130, 79), (40, 9, 82), (20, 4, 6),
+                                 (64, 40, 128), (130, 3, 200), (260, 150, 111)])
 def test_vadv_vs_oracle(dom, variant):
     f = gen.vadv_inputs(*dom, seed=99)
     ref = oracle.vadv(f["utens_stage"].copy(), f["u_stage"], f["wcon"], f["u_pos"], f["utens"],
