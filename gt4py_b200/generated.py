@@ -220,7 +220,8 @@ class GeneratedStencil(StencilObject):
                 continue
             smem, sfx = 0, ("_u" if unit else "")
             if k["kind"] == "point":
-                block, grid = (64, 4, 1), ((wi + 63) // 64, (wj + 3) // 4, nk)
+                rows = 4 * int(k.get("rows_per_thread", 1))  # rows of the compute block a CTA covers
+                block, grid = (64, 4, 1), ((wi + 63) // 64, (wj + rows - 1) // rows, nk)
             elif k["kind"] == "tile":  # a CTA per TI x TJ tile of the compute domain and level; halo recomputed
                 ti, tj = k["tile"]
                 block, grid, smem = (*k["block"], 1), ((ni + ti - 1) // ti, (nj + tj - 1) // tj, nk), k["smem_bytes"]
