@@ -103,6 +103,7 @@ class B200Backend(BaseBackend):
         "device_sync": {"versioning": True, "type": bool},
         "use_library_kernels": {"versioning": True, "type": bool},
         "fuse_temporaries": {"versioning": True, "type": bool},
+        "k_register_cache": {"versioning": True, "type": bool},
     }
     storage_info: ClassVar[layout.LayoutInfo] = {
         "alignment": storage.ALIGNMENT,
@@ -158,13 +159,14 @@ class B200Backend(BaseBackend):
 
     def make_plan(self):
         name, fuse = self.builder.options.name, self.fuse
+        kc = bool(self.builder.options.backend_opts.get("k_register_cache", False))
         if fuse is None or fuse:
-            plan, source = lowering.lower(self.oir(True), name, fuse=True)
+            plan, source = lowering.lower(self.oir(True), name, fuse=True, k_register_cache=kc)
             deepest = max([k.get("stages", 0) for k in plan["kernels"]], default=0)
             if fuse is None and deepest < self.AUTO_FUSE_MIN_STAGES:
                 fuse = False
         if fuse is not None and not fuse:
-            plan, source = lowering.lower(self.oir(False), name, fuse=False)
+            plan, source = lowering.lower(self.oir(False), name, fuse=False, k_register_cache=kc)
         match = self.library_match()
         if match is not None:
             plan["library"] = match

@@ -80,6 +80,10 @@ def definitions():
         defs[name + "__tile"] = (*defs[name][:2], {"fuse_temporaries": True})
     for name in ("fv3_chain", "exec_info_diffusion"):
         defs[name + "__point"] = (*defs[name][:2], {"fuse_temporaries": False})
+    # column kernels with the K register cache (rolling buffer) switched on; library matching off so that the
+    # lowered kernels are what runs
+    for name in ("vertical_advection_dycore", "tridiagonal_solver", "column_physics", "while_stencil"):
+        defs[name + "__kcache"] = (*defs[name][:2], {"k_register_cache": True, "use_library_kernels": False})
     # float32 variants of the headline stencils (north_star tolerance for float32: 1e-5; these are bit-exact):
     # the same definitions re-annotated the way the reference's suites do it (testing/utils.py:24-30)
     import inspect
