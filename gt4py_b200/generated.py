@@ -228,12 +228,17 @@ class GeneratedStencil(StencilObject):
                 if tma_ok.get(k["name"]):
                     sfx, smem = "_t", k["tma"]["smem_bytes"]
             else:
-                block, grid = (32, 4, 1), ((wi + 31) // 32, (wj + 3) // 4, 1)
+                bx, by = _COLUMN_BLOCK
+                block, grid = (bx, by, 1), ((wi + bx - 1) // bx, (wj + by - 1) // by, 1)
             if nk <= 0 and k["kind"] != "column":
                 continue
             cls._last_entry_points.append(k["name"] + sfx)
             _lib.check(_lib.lib().b200_launch(mod.kernels[k["name"] + sfx], (ctypes.c_uint32 * 3)(*grid),
                                               (ctypes.c_uint32 * 3)(*block), smem, sh, argp, 1))
+
+
+# threads of a column-kernel CTA along I x J (a thread per column); tuning hook B200_COLUMN_BLOCK=IxJ
+_COLUMN_BLOCK = tuple(int(x) for x in os.environ.get("B200_COLUMN_BLOCK", "32x4").split("x"))
 
 
 def stencil_class(plan: Dict[str, Any], directory: str):
