@@ -1,0 +1,148 @@
+"""TEST INFRASTRUCTURE: run the generated `point` / `column` kernels of a plan ON THE HOST, to check the
+OIR -> CUDA lowering (gt4py_b200/lowering.py) against the reference-made golden outputs without a GPU.
+
+The committed `kernel.cu` is compiled as plain C++ with g++: the CUDA qualifiers are defined away, blockIdx /
+blockDim / threadIdx become thread-local globals, and a launcher per kernel loops over the grid and the block
+sequentially (legal for these two templates: their threads never communicate).  `tile` kernels (shared memory,
+__syncthreads, TMA) are not emulated; plans that contain one are skipped.  Arithmetic is IEEE on both sides
+(-ffp-contract=off here, -fmad=false on the device), so the comparison is bit-exact like the GPU tests.
+
+Nothing here is used by the product: gt4py_b200 has no CPU path.
+"""
+from __future__ import annotations
+
+import ctypes
+import hashlib
+import json
+import os
+import subprocess
+import tempfile
+
+import numpy as np
+
+from gt4py_b200 import generated
+
+SHIM = r"""
+#include <cstdint>
+#include <cmath>
+#include <cstdlib>
+#define __device__
+#define __global__
+#define __forceinline__ inline
+#define __restrict__ __restrict
+#define __launch_bounds__(...)
+using std::isnan; using std::isinf; using std::isfinite;
+struct emu_dim3 { unsigned x, y, z; };
+static thread_local emu_dim3 blockIdx, blockDim, threadIdx;
+"""
+
+LAUNCHER = r"""
+extern "C" void emu_{name}(const Args *a, unsigned gx, unsigned gy, unsigned gz, unsigned bx, unsigned by, unsigned bz)
+{{
+    blockDim = emu_dim3{{bx, by, bz}};
+    for (unsigned Z = 0; Z < gz; ++Z) for (unsigned Y = 0; Y < gy; ++Y) for (unsigned X = 0; X < gx; ++X) {{
+        blockIdx = emu_dim3{{X, Y, Z}};
+        for (unsigned z = 0; z < bz; ++z) for (unsigned y = 0; y < by; ++y) for (unsigned x = 0; x < bx; ++x) {{
+            threadIdx = emu_dim3{{x, y, z}};
+            {name}(*a);
+        }}
+    }}
+}}
+"""
+
+
+def emulable(plan) -> bool:
+    return all(k["kind"] in ("point", "column") for k in plan["kernels"])
+
+
+def _host_source(src: str, plan) -> str:
+    # drop the TMA plumbing (inline PTX) that only the tile kernels' <k>_t entry points use
+    a = src.index("// TMA plumbing")
+    b = src.index("struct Args {")
+    body = src[:a] + src[b:]
+    body = body.replace("#include <cstdint>\n#include <cmath>\n", "", 1)
+    out = SHIM + body
+    for k in plan["kernels"]:
+        out += LAUNCHER.format(name=k["name"])  # the generic-stride entry point: host arrays keep numpy's strides
+    return out
+
+
+def build(plan_dir: str):
+    with open(os.path.join(plan_dir, "plan.json")) as fh:
+        plan = json.load(fh)
+    with open(os.path.join(plan_dir, plan.get("source", "kernel.cu"))) as fh:
+        text = _host_source(fh.read(), plan)
+    cache = os.path.join(tempfile.gettempdir(), "gt4py_b200_host_emulation")
+    os.makedirs(cache, exist_ok=True)
+    tag = hashlib.sha256(text.encode()).hexdigest()[:16]
+    lib = os.path.join(cache, f"emu_{tag}.so")
+    if not os.path.exists(lib):
+        cpp = os.path.join(cache, f"emu_{tag}.cpp")
+        with open(cpp, "w") as fh:
+            fh.write(text)
+        cmd = ["g++", "-std=c++17", "-O1", "-ffp-contract=off", "-fno-fast-math", "-shared", "-fPIC", "-w", cpp, "-o",
+               lib + ".tmp"]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode:
+            raise RuntimeError(f"g++ failed on the host form of {plan_dir}:\n{r.stderr[:4000]}")
+        os.replace(lib + ".tmp", lib)
+    return plan, ctypes.CDLL(lib)
+
+
+def run(plan_dir: str, fields: dict, params: dict, origins: dict, domain):
+    """fields: name -> numpy array (modified in place) or None; origins: name -> index of the compute origin."""
+    plan, lib = build(plan_dir)
+    Args = generated._args_struct(plan)
+    a = Args()
+    ni, nj, nk = (int(x) for x in domain)
+    a.ni, a.nj, a.nk = ni, nj, nk
+    keep = []
+    for spec in plan["fields"]:
+        name = spec["name"]
+        arr = fields.get(name)
+        if arr is None:
+            setattr(a, name, None)
+            continue
+        item = arr.dtype.itemsize
+        strides, ptr, pos = [0, 0, 0], arr.ctypes.data, 0
+        for d in range(3):
+            if spec["dims"][d]:
+                strides[d] = arr.strides[pos] // item
+                ptr += int(origins[name][pos]) * arr.strides[pos]
+                pos += 1
+        strides += [arr.strides[pos + n] // item for n in range(len(spec["data_dims"]))]
+        setattr(a, name, ptr)
+        getattr(a, name + "_s")[:] = strides
+    for t in plan["temporaries"]:  # same shapes / origins as generated.GeneratedStencil._temporaries
+        (li, hi), (lj, hj) = t["pad"]
+        shape = [ni + li + hi if t["dims"][0] else 1, nj + lj + hj if t["dims"][1] else 1,
+                 nk if t["dims"][2] else 1] + list(t["data_dims"])
+        arr = np.zeros(shape, dtype=np.dtype(t["dtype"]), order="F")
+        keep.append(arr)
+        item = arr.dtype.itemsize
+        strides = [s // item for s in arr.strides]
+        for d in range(3):
+            if not t["dims"][d]:
+                strides[d] = 0
+        ptr = arr.ctypes.data + (li * arr.strides[0] if t["dims"][0] else 0) + (lj * arr.strides[1] if t["dims"][1] else 0)
+        setattr(a, t["name"], ptr)
+        getattr(a, t["name"] + "_s")[:] = strides
+    for s in plan["scalars"]:
+        setattr(a, s["name"], params[s["name"]])
+    for k in plan["kernels"]:  # launch geometry of generated.GeneratedStencil._launch
+        wi = ni + k["i_ext"][1] - k["i_ext"][0]
+        wj = nj + k["j_ext"][1] - k["j_ext"][0]
+        if wi <= 0 or wj <= 0:
+            continue
+        if k["kind"] == "point":
+            rows = 4 * int(k.get("rows_per_thread", 1))
+            block, grid = (64, 4, 1), ((wi + 63) // 64, (wj + rows - 1) // rows, nk)
+            if nk <= 0:
+                continue
+        else:
+            block, grid = (32, 4, 1), ((wi + 31) // 32, (wj + 3) // 4, 1)
+        fn = getattr(lib, "emu_" + k["name"])
+        fn.argtypes = [ctypes.c_void_p] + [ctypes.c_uint] * 6
+        fn.restype = None
+        fn(ctypes.byref(a), *grid, *block)
+    return fields

@@ -308,3 +308,33 @@ def test_fv3_chain_entry_points_agree(mode, monkeypatch):
         st(d["phi"], d["u"], d["v"], out, dt=0.05, alpha=0.03, origin={"_all_": (h, h, 0), "out": (0, 0, 0)}, domain=domain)
     assert np.array_equal(out.asnumpy(), want)
     assert type(st)._last_entry_points == [{"tma": "k0_0_t", "unit": "k0_0_u", "generic": "k0_0"}[mode]]
+
+
+# ---- CPU: the point / column lowerings executed on the host against the reference-made golden outputs --------------
+def _host_emulable():
+    from tests import host_emulation
+
+    return [n for n in NAMES if host_emulation.emulable(_plan(n))]
+
+
+@pytest.mark.parametrize("name", _host_emulable())
+def test_lowered_point_and_column_kernels_on_the_host(name):
+    """The committed kernel.cu compiled as plain C++ (tests/host_emulation.py) and run thread by thread must
+    reproduce the outputs of the reference's numpy backend -- the same bar as the GPU test, reachable without
+    a GPU.  Checks the lowering (indexing, guards, row march, two-level column trips, K register cache), not the
+    device; tile kernels are GPU-only."""
+    from tests import host_emulation
+
+    case, g = _case(name)
+    fields = {}
+    for f in _plan(name)["fields"]:
+        n = f["name"]
+        fields[n] = None if n in case["none_fields"] else np.array(g["in__" + n], order="F")
+    params = {k[len("param__"):]: g[k][()] for k in g.files if k.startswith("param__")}
+    host_emulation.run(os.path.join(GEN, name), fields, params, case["origins"], case["domain"])
+    for n in case["written"]:
+        got, want = fields[n], g["out__" + n]
+        if name in TOLERANT:
+            np.testing.assert_allclose(got, want, rtol=TOLERANT[name], atol=1e-300, equal_nan=True, err_msg=n)
+        else:
+            assert np.array_equal(got, want, equal_nan=got.dtype.kind == "f"), (name, n)
