@@ -3,8 +3,9 @@ OIR -> CUDA lowering (gt4py_b200/lowering.py) against the reference-made golden 
 
 The committed `kernel.cu` is compiled as plain C++ with g++: the CUDA qualifiers are defined away, blockIdx /
 blockDim / threadIdx become thread-local globals, and a launcher per kernel loops over the grid and the block
-sequentially (legal for these two templates: their threads never communicate).  `tile` kernels (shared memory,
-__syncthreads, TMA) are not emulated; plans that contain one are skipped.  Arithmetic is IEEE on both sides
+sequentially (legal for these two templates: their threads never communicate).  `tile` kernels run through their
+plain entry point (no TMA): one CTA at a time, one OS thread per CUDA thread, `__syncthreads()` = a std::barrier,
+the dynamic shared memory a static buffer.  Arithmetic is IEEE on both sides
 (-ffp-contract=off here, -fmad=false on the device), so the comparison is bit-exact like the GPU tests.
 
 Nothing here is used by the product: gt4py_b200 has no CPU path.
@@ -15,6 +16,7 @@ import ctypes
 import hashlib
 import json
 import os
+import re
 import subprocess
 import tempfile
 
@@ -26,14 +28,42 @@ SHIM = r"""
 #include <cstdint>
 #include <cmath>
 #include <cstdlib>
+#include <barrier>
+#include <thread>
+#include <vector>
 #define __device__
 #define __global__
 #define __forceinline__ inline
 #define __restrict__ __restrict
 #define __launch_bounds__(...)
-using std::isnan; using std::isinf; using std::isfinite;
+#include <algorithm>
+using std::isnan; using std::isinf; using std::isfinite; using std::min; using std::max;
 struct emu_dim3 { unsigned x, y, z; };
 static thread_local emu_dim3 blockIdx, blockDim, threadIdx;
+#define __shared__ static
+#define __align__(x) alignas(x)
+alignas(1024) static unsigned char emu_smem[256 * 1024];
+static std::barrier<> *emu_barrier = nullptr;
+#define __syncthreads() emu_barrier->arrive_and_wait()
+"""
+
+TILE_LAUNCHER = r"""
+extern "C" void emu_{name}(const Args *a, unsigned gx, unsigned gy, unsigned gz, unsigned bx, unsigned by, unsigned bz)
+{{
+    for (unsigned Z = 0; Z < gz; ++Z) for (unsigned Y = 0; Y < gy; ++Y) for (unsigned X = 0; X < gx; ++X) {{
+        std::barrier<> bar((std::ptrdiff_t)(bx * by * bz));
+        emu_barrier = &bar;
+        std::vector<std::thread> pool;
+        for (unsigned z = 0; z < bz; ++z) for (unsigned y = 0; y < by; ++y) for (unsigned x = 0; x < bx; ++x)
+            pool.emplace_back([=] {{
+                blockDim = emu_dim3{{bx, by, bz}};
+                blockIdx = emu_dim3{{X, Y, Z}};
+                threadIdx = emu_dim3{{x, y, z}};
+                {name}(*a);
+            }});
+        for (auto &t : pool) t.join();
+    }}
+}}
 """
 
 LAUNCHER = r"""
@@ -52,7 +82,7 @@ extern "C" void emu_{name}(const Args *a, unsigned gx, unsigned gy, unsigned gz,
 
 
 def emulable(plan) -> bool:
-    return all(k["kind"] in ("point", "column") for k in plan["kernels"])
+    return all(k["kind"] in ("point", "column", "tile") for k in plan["kernels"])
 
 
 def _host_source(src: str, plan) -> str:
@@ -61,9 +91,15 @@ def _host_source(src: str, plan) -> str:
     b = src.index("struct Args {")
     body = src[:a] + src[b:]
     body = body.replace("#include <cstdint>\n#include <cmath>\n", "", 1)
+    # the <k>_t entry points (TMA-staged inputs) are device-only
+    body = re.sub(r"__device__ __forceinline__ void (\w+)_tma_impl\(const Args &a\).*?\n"
+                  r"extern \"C\" __global__ void __launch_bounds__\(\d+\) \1_t\(const Args a\)[^\n]*\n?", "", body,
+                  flags=re.S)
+    body = re.sub(r"extern __shared__ __align__\(\d+\) unsigned char b200_smem\[\];",
+                  "unsigned char *b200_smem = emu_smem;", body)
     out = SHIM + body
-    for k in plan["kernels"]:
-        out += LAUNCHER.format(name=k["name"])  # the generic-stride entry point: host arrays keep numpy's strides
+    for k in plan["kernels"]:  # the generic-stride entry point: host arrays keep numpy's strides
+        out += (TILE_LAUNCHER if k["kind"] == "tile" else LAUNCHER).format(name=k["name"])
     return out
 
 
@@ -80,8 +116,8 @@ def build(plan_dir: str):
         cpp = os.path.join(cache, f"emu_{tag}.cpp")
         with open(cpp, "w") as fh:
             fh.write(text)
-        cmd = ["g++", "-std=c++17", "-O1", "-ffp-contract=off", "-fno-fast-math", "-shared", "-fPIC", "-w", cpp, "-o",
-               lib + ".tmp"]
+        cmd = ["g++", "-std=c++20", "-O1", "-ffp-contract=off", "-fno-fast-math", "-shared", "-fPIC", "-pthread", "-w", cpp,
+               "-o", lib + ".tmp"]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode:
             raise RuntimeError(f"g++ failed on the host form of {plan_dir}:\n{r.stderr[:4000]}")
@@ -137,6 +173,11 @@ def run(plan_dir: str, fields: dict, params: dict, origins: dict, domain):
         if k["kind"] == "point":
             rows = 4 * int(k.get("rows_per_thread", 1))
             block, grid = (64, 4, 1), ((wi + 63) // 64, (wj + rows - 1) // rows, nk)
+            if nk <= 0:
+                continue
+        elif k["kind"] == "tile":
+            ti, tj = k["tile"]
+            block, grid = (*k["block"], 1), ((ni + ti - 1) // ti, (nj + tj - 1) // tj, nk)
             if nk <= 0:
                 continue
         else:

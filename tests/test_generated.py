@@ -318,11 +318,12 @@ def _host_emulable():
 
 
 @pytest.mark.parametrize("name", _host_emulable())
-def test_lowered_point_and_column_kernels_on_the_host(name):
+def test_lowered_kernels_on_the_host(name):
     """The committed kernel.cu compiled as plain C++ (tests/host_emulation.py) and run thread by thread must
     reproduce the outputs of the reference's numpy backend -- the same bar as the GPU test, reachable without
-    a GPU.  Checks the lowering (indexing, guards, row march, two-level column trips, K register cache), not the
-    device; tile kernels are GPU-only."""
+    a GPU.  Checks the lowering (indexing, guards, row marches, two-level column trips, K register cache, the
+    shared-memory stages of the tile kernels through their plain entry point), not the device; the TMA-staged
+    entry points are GPU-only."""
     from tests import host_emulation
 
     case, g = _case(name)
