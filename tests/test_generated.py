@@ -341,12 +341,16 @@ def test_lowered_kernels_on_the_host(name):
             assert np.array_equal(got, want, equal_nan=got.dtype.kind == "f"), (name, n)
 
 
-@pytest.mark.parametrize("domain", [(5, 3, 7), (66, 19, 5), (130, 35, 4), (64, 16, 6), (1, 1, 5)])
-@pytest.mark.parametrize("name", ["fv3_chain", "horizontal_diffusion", "horizontal_diffusion__tile",
-                                  "vertical_advection_dycore", "tridiagonal_solver", "column_physics",
-                                  "column_physics__kcache", "exec_info_advection", "exec_info_diffusion",
-                                  "horizontal_regions", "horizontal_region_with_conditional__tile",
-                                  "fv3_chain__f32lit"])
+_SIZES = [(5, 3, 7), (66, 19, 5), (130, 35, 4), (64, 16, 6), (1, 1, 5)]
+_SIZED = ["fv3_chain", "horizontal_diffusion", "horizontal_diffusion__tile", "vertical_advection_dycore",
+          "tridiagonal_solver", "column_physics", "column_physics__kcache", "exec_info_advection",
+          "exec_info_diffusion", "horizontal_regions", "horizontal_region_with_conditional__tile", "fv3_chain__f32lit"]
+# ... and every other definition of the registry fixtures once, at a ragged size
+_CASES = [(n, d) for n in _SIZED for d in _SIZES] + [(n, (67, 9, 7)) for n in NAMES
+                                                      if not n.startswith("suite_") and n not in _SIZED]
+
+
+@pytest.mark.parametrize("name,domain", _CASES)
 def test_lowering_against_the_reference_at_other_sizes(name, domain):
     """Differential test in the build container: the reference's numpy backend and the host-emulated kernels of a
     FRESH lowering on the same seeded inputs, at sizes that cross tile / block / row-march boundaries (the
