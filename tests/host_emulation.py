@@ -42,14 +42,33 @@ struct emu_dim3 { unsigned x, y, z; };
 static thread_local emu_dim3 blockIdx, blockDim, threadIdx;
 #define __shared__ static
 #define __align__(x) alignas(x)
-alignas(1024) static unsigned char emu_smem[256 * 1024];
+#include <sys/mman.h>
+static unsigned char *emu_smem = nullptr;  // the CTA's dynamic shared-memory window, fenced by guard pages
 static std::barrier<> *emu_barrier = nullptr;
+// Map `bytes` of shared memory between two inaccessible pages; mode 0: the window starts right after the front
+// guard, mode 1: it ends (to 16 bytes) right before the back guard -- a read outside the window the plan asked
+// for (plan["kernels"][..]["smem_bytes"]) is a segmentation fault here instead of a silent stray read.
+static unsigned char *emu_map_window(size_t bytes, int mode, void **base, size_t *total)
+{
+    const size_t page = 4096, body = (bytes + page - 1) / page * page;
+    *total = body + 2 * page;
+    unsigned char *p = (unsigned char *)mmap(nullptr, *total, PROT_READ | PROT_WRITE, MAP_PRIVATE | MAP_ANONYMOUS, -1, 0);
+    if (p == MAP_FAILED) abort();
+    mprotect(p, page, PROT_NONE);
+    mprotect(p + page + body, page, PROT_NONE);
+    *base = p;
+    return p + page + (mode ? (body - bytes) / 16 * 16 : 0);
+}
 #define __syncthreads() emu_barrier->arrive_and_wait()
 """
 
 TILE_LAUNCHER = r"""
-extern "C" void emu_{name}(const Args *a, unsigned gx, unsigned gy, unsigned gz, unsigned bx, unsigned by, unsigned bz)
+extern "C" void emu_{name}(const Args *a, unsigned gx, unsigned gy, unsigned gz, unsigned bx, unsigned by, unsigned bz,
+                           unsigned smem_bytes, int mode)
 {{
+    void *base;
+    size_t total;
+    emu_smem = emu_map_window(smem_bytes, mode, &base, &total);
     for (unsigned Z = 0; Z < gz; ++Z) for (unsigned Y = 0; Y < gy; ++Y) for (unsigned X = 0; X < gx; ++X) {{
         std::barrier<> bar((std::ptrdiff_t)(bx * by * bz));
         emu_barrier = &bar;
@@ -63,6 +82,7 @@ extern "C" void emu_{name}(const Args *a, unsigned gx, unsigned gy, unsigned gz,
             }});
         for (auto &t : pool) t.join();
     }}
+    munmap(base, total);
 }}
 """
 
@@ -125,8 +145,9 @@ def build(plan_dir: str):
     return plan, ctypes.CDLL(lib)
 
 
-def run(plan_dir: str, fields: dict, params: dict, origins: dict, domain):
-    """fields: name -> numpy array (modified in place) or None; origins: name -> index of the compute origin."""
+def run(plan_dir: str, fields: dict, params: dict, origins: dict, domain, window_mode: int = 0):
+    """fields: name -> numpy array (modified in place) or None; origins: name -> index of the compute origin.
+    window_mode: where the tile kernels' shared-memory window sits between its guard pages (0 front, 1 back)."""
     plan, lib = build(plan_dir)
     Args = generated._args_struct(plan)
     a = Args()
@@ -183,7 +204,11 @@ def run(plan_dir: str, fields: dict, params: dict, origins: dict, domain):
         else:
             block, grid = (32, 4, 1), ((wi + 31) // 32, (wj + 3) // 4, 1)
         fn = getattr(lib, "emu_" + k["name"])
-        fn.argtypes = [ctypes.c_void_p] + [ctypes.c_uint] * 6
         fn.restype = None
-        fn(ctypes.byref(a), *grid, *block)
+        if k["kind"] == "tile":
+            fn.argtypes = [ctypes.c_void_p] + [ctypes.c_uint] * 7 + [ctypes.c_int]
+            fn(ctypes.byref(a), *grid, *block, int(k["smem_bytes"]), int(window_mode))
+        else:
+            fn.argtypes = [ctypes.c_void_p] + [ctypes.c_uint] * 6
+            fn(ctypes.byref(a), *grid, *block)
     return fields
