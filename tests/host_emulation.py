@@ -19,6 +19,7 @@ import os
 import re
 import subprocess
 import tempfile
+import threading
 
 import numpy as np
 
@@ -133,15 +134,18 @@ def build(plan_dir: str):
     tag = hashlib.sha256(text.encode()).hexdigest()[:16]
     lib = os.path.join(cache, f"emu_{tag}.so")
     if not os.path.exists(lib):
-        cpp = os.path.join(cache, f"emu_{tag}.cpp")
+        uniq = f"{os.getpid()}_{threading.get_ident()}"  # two plans with identical kernels may build concurrently
+        cpp = os.path.join(cache, f"emu_{tag}_{uniq}.cpp")
+        tmp = os.path.join(cache, f"emu_{tag}_{uniq}.so")
         with open(cpp, "w") as fh:
             fh.write(text)
         cmd = ["g++", "-std=c++20", "-O1", "-ffp-contract=off", "-fno-fast-math", "-shared", "-fPIC", "-pthread", "-w", cpp,
-               "-o", lib + ".tmp"]
+               "-o", tmp]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode:
             raise RuntimeError(f"g++ failed on the host form of {plan_dir}:\n{r.stderr[:4000]}")
-        os.replace(lib + ".tmp", lib)
+        os.replace(tmp, lib)
+        os.remove(cpp)
     return plan, ctypes.CDLL(lib)
 
 

@@ -317,8 +317,19 @@ def _host_emulable():
     return [n for n in NAMES if host_emulation.emulable(_plan(n))]
 
 
+@pytest.fixture(scope="module")
+def _host_libraries():
+    """g++ over all fixture kernels up front, in parallel (each is cached by source hash under the temp dir)."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    from tests import host_emulation
+
+    with ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 1)) as pool:
+        list(pool.map(lambda n: host_emulation.build(os.path.join(GEN, n)), _host_emulable()))
+
+
 @pytest.mark.parametrize("name", _host_emulable())
-def test_lowered_kernels_on_the_host(name):
+def test_lowered_kernels_on_the_host(name, _host_libraries):
     """The committed kernel.cu compiled as plain C++ (tests/host_emulation.py) and run thread by thread must
     reproduce the outputs of the reference's numpy backend -- the same bar as the GPU test, reachable without
     a GPU.  Checks the lowering (indexing, guards, row marches, two-level column trips, K register cache, the
