@@ -84,6 +84,7 @@ _VP = c_void_p
 _PROTOTYPES = {
     "b200_abi_version": ([], c_int),
     "b200_last_error": ([], c_char_p),
+    "b200_last_kernel": ([], c_char_p),
     "b200_device_count": ([POINTER(c_int)], c_int),
     "b200_set_device": ([c_int], c_int),
     "b200_get_device": ([POINTER(c_int)], c_int),
@@ -163,6 +164,11 @@ def check(code: int):
     if code != 0:
         msg = lib().b200_last_error()
         raise B200Error(code, msg.decode("utf-8", "replace") if msg else "")
+
+
+def last_kernel() -> str:
+    """Name of the kernel the last library-stencil call of this thread launched."""
+    return (lib().b200_last_kernel() or b"").decode()
 
 
 def device_count() -> int:

@@ -90,7 +90,11 @@ def _call_run(self, field_args, parameter_args, domain, origin, *, validate_args
     def generate_implementation(self) -> str:
         names = [n for n in self.args_data.field_info] + [n for n in self.args_data.parameter_info]
         kwargs = ", ".join(f"{n}={n}" for n in names)
-        return f"type(self)._b200().run(_domain_=_domain_, _origin_=_origin_, exec_info=None, {kwargs})"
+        sync = self.builder.options.backend_opts.get("device_sync", True)
+        note = ("# device_sync=True: run() returns after the stream has been synchronised (b200_stream_sync / "
+                "b200_device_sync) --\n# this backend's counterpart of cupy.cuda.Device(0).synchronize() "
+                "(gtc_common.py:288-296)\n" if sync else "# device_sync=False: run() returns after the launch\n")
+        return note + f"type(self)._b200().run(_domain_=_domain_, _origin_=_origin_, exec_info=None, {kwargs})"
 
 
 class B200Backend(BaseBackend):
@@ -200,5 +204,49 @@ class B200Backend(BaseBackend):
         return {**super().extra_cache_info, "plan_md5": self.builder.backend_data.get("b200:plan_md5", "")}
 
 
+def install_storage_hooks() -> bool:
+    """``gt4py.storage.{empty, zeros, ones, full, from_array}(backend="b200")`` without cupy.
+
+    The reference allocates every ``device == "gpu"`` storage through cupy (storage/cartesian/utils.py:258-276:
+    ``allocate_gpu`` asserts it, ``asarray(..., device="gpu")`` is ``cupy.asarray``, interface.py:81-86, :325).  When
+    the reference found no cupy at import, this installs cupy-free replacements for exactly those two functions:
+    the same padded / aligned allocation algorithm (gt4py_b200.storage.allocate, after allocators.py:189-275) over
+    cudaMalloc, returning ``gt4py_b200.storage.DeviceArray`` (``__cuda_array_interface__`` v3).  With a real cupy the
+    reference's own path is left alone (cupy arrays expose ``__cuda_array_interface__``, which is all the kernels need).
+    """
+    import numpy as np
+    from gt4py.storage.cartesian import utils as storage_utils
+
+    cp = getattr(storage_utils, "cp", None)
+    if cp is not None and not getattr(cp, "__gt4py_b200_standin__", False):
+        return False
+    if getattr(storage_utils.allocate_gpu, "__gt4py_b200__", False):
+        return True
+
+    def allocate_gpu(shape, layout_map, dtype, alignment_bytes, aligned_index):
+        shape = tuple(int(x) for x in shape)
+        arr = storage.allocate(shape, tuple(int(x) for x in layout_map), np.dtype(dtype), int(alignment_bytes),
+                               tuple(int(x) for x in (aligned_index or (0,) * len(shape))))
+        return arr._buf, arr
+
+    reference_asarray = storage_utils.asarray
+
+    def asarray(array, *, device=None):
+        if hasattr(array, "ndarray"):
+            array = array.ndarray
+        if isinstance(array, storage.DeviceArray):
+            return array.asnumpy() if device == "cpu" else array
+        if device == "gpu" or (device is None and hasattr(array, "__cuda_array_interface__")
+                               and not hasattr(array, "__array_interface__")):
+            return storage.as_device_array(array)
+        return reference_asarray(array, device=device)
+
+    allocate_gpu.__gt4py_b200__ = True
+    storage_utils.allocate_gpu = allocate_gpu
+    storage_utils.asarray = asarray
+    return True
+
+
 if NAME not in gt_backend.REGISTRY:
     gt_backend.register(B200Backend)
+install_storage_hooks()

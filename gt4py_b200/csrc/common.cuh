@@ -12,6 +12,9 @@
 namespace b200 {
 
 void set_error(const char *fmt, ...);
+// name of the kernel a library entry point (b200_hdiff / b200_vadv / b200_tridiag) is about to launch on this
+// thread: b200_last_kernel() reports it, so that measurements name what really ran
+void note_kernel(const char *name);
 
 #define B200_CUDA_CHECK(expr)                                                              \
     do {                                                                                   \

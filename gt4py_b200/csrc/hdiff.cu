@@ -316,6 +316,7 @@ static int launch_hdiff(View3<const T> in, View3<T> out, View3<const T> co, cons
     if (variant == 1) {
         dim3 block(64, 4, 1);
         dim3 grid((ni + 63) / 64, (nj + 3) / 4, nk);
+        note_kernel("hdiff_point");
         hdiff_point<LIMITER, T><<<grid, block, 0, stream>>>(in, out, co, ni, nj, nk);
     } else if (variant >= 2 && variant <= 4) {
         if (!fast_ok) {
@@ -337,11 +338,11 @@ static int launch_hdiff(View3<const T> in, View3<T> out, View3<const T> co, cons
         dim3 block(32 * wpb, 1, 1);
         dim3 grid((nwarps + wpb - 1) / wpb, (nj + tj - 1) / tj, nk);
         if (variant == 2)
-            hdiff_jmarch<LIMITER, 2, T><<<grid, block, 0, stream>>>(in, out, co, ni, nj, nk, tj);
+            hdiff_jmarch<LIMITER, 2, T><<<grid, block, 0, stream>>>(in, out, co, ni, nj, nk, tj), note_kernel("hdiff_jmarch");
         else if (variant == 3)
-            hdiff_jmarch<LIMITER, 4, T><<<grid, block, 0, stream>>>(in, out, co, ni, nj, nk, tj);
+            hdiff_jmarch<LIMITER, 4, T><<<grid, block, 0, stream>>>(in, out, co, ni, nj, nk, tj), note_kernel("hdiff_jmarch");
         else if constexpr (F64)  // variant 4: alternating march directions (less DRAM traffic, not faster: DESIGN.md 3.1)
-            hdiff_jmarch_alt<LIMITER, 2, 4><<<grid, block, 0, stream>>>(in, out, co, ni, nj, nk, tj);
+            hdiff_jmarch_alt<LIMITER, 2, 4><<<grid, block, 0, stream>>>(in, out, co, ni, nj, nk, tj), note_kernel("hdiff_jmarch_alt");
     } else if (variant == 5) {
         if constexpr (F64) {
             bool handled = false;

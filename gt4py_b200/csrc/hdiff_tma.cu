@@ -170,6 +170,7 @@ int launch_cfg(const View3<const double> &in, const View3<double> &out, const Vi
     auto kern = hdiff_tma_kernel<LIMITER, NW, RS>;
     B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid((ni + G::OUT_COLS - 1) / G::OUT_COLS, (nj + cj - 1) / cj, nk);
+    note_kernel("hdiff_tma_kernel");
     kern<<<grid, 32 * (NW + 1), smem, stream>>>(m_in, m_co, out, ni, nj, cj, NS);
     B200_CUDA_CHECK(cudaGetLastError());
     return B200_OK;

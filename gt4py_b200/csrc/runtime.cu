@@ -12,12 +12,15 @@ void set_error(const char *fmt, ...)
     vsnprintf(g_err, sizeof(g_err), fmt, ap);
     va_end(ap);
 }
+static thread_local const char *g_kernel = "";
+void note_kernel(const char *name) { g_kernel = name; }
 }  // namespace b200
 
 extern "C" {
 
 int b200_abi_version(void) { return B200_ABI_VERSION; }
 const char *b200_last_error(void) { return b200::g_err; }
+const char *b200_last_kernel(void) { return b200::g_kernel; }
 
 int b200_device_count(int *count)
 {
@@ -116,6 +119,9 @@ int b200_memset(void *dst, int value, size_t bytes, void *stream)
 {
     if (bytes == 0) return B200_OK;
     B200_CUDA_CHECK(cudaMemsetAsync(dst, value, bytes, (cudaStream_t)stream));
+    // null stream: finished on return, like the copies above (the library's own streams are non-blocking and do
+    // not order against the legacy default stream)
+    if (!stream) B200_CUDA_CHECK(cudaStreamSynchronize(0));
     return B200_OK;
 }
 

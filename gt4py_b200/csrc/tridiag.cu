@@ -196,14 +196,14 @@ extern "C" int b200_tridiag(const b200_field *inf, const b200_field *diag, const
         }
     }
     switch (variant) {
-    case 1: tridiag_column<4><<<grid, 128, 0, st>>>(a); break;
-    case 2: tridiag_column_q<4, 4, 8><<<grid, 128, 0, st>>>(a); break;
-    case 3: tridiag_column_q<6, 4, 6><<<grid, 128, 0, st>>>(a); break;
-    case 4: tridiag_column_q<8, 8, 4><<<grid, 128, 0, st>>>(a); break;
-    case 5: tridiag_column_q<4, 8, 8><<<grid, 128, 0, st>>>(a); break;
-    case 6: tridiag_column_q<3, 4, 10><<<grid, 128, 0, st>>>(a); break;
-    case 7: tridiag_column_q<2, 4, 12><<<grid, 128, 0, st>>>(a); break;
-    default: tridiag_column_q<3, 4, 10><<<grid, 128, 0, st>>>(a); break;  // variant 0 = 6, the fastest measured
+    case 1: note_kernel("tridiag_column"); tridiag_column<4><<<grid, 128, 0, st>>>(a); break;
+    case 2: note_kernel("tridiag_column_q"); tridiag_column_q<4, 4, 8><<<grid, 128, 0, st>>>(a); break;
+    case 3: note_kernel("tridiag_column_q"); tridiag_column_q<6, 4, 6><<<grid, 128, 0, st>>>(a); break;
+    case 4: note_kernel("tridiag_column_q"); tridiag_column_q<8, 8, 4><<<grid, 128, 0, st>>>(a); break;
+    case 5: note_kernel("tridiag_column_q"); tridiag_column_q<4, 8, 8><<<grid, 128, 0, st>>>(a); break;
+    case 6: note_kernel("tridiag_column_q"); tridiag_column_q<3, 4, 10><<<grid, 128, 0, st>>>(a); break;
+    case 7: note_kernel("tridiag_column_q"); tridiag_column_q<2, 4, 12><<<grid, 128, 0, st>>>(a); break;
+    default: note_kernel("tridiag_column_q"); tridiag_column_q<3, 4, 10><<<grid, 128, 0, st>>>(a); break;  // variant 0 = 6, the fastest measured
     }
     B200_CUDA_CHECK(cudaGetLastError());
     return B200_OK;

@@ -309,6 +309,7 @@ static int launch_tri(const TriFArgs &a, cudaStream_t stream, bool *handled)
     const int grid = ntiles < sms ? ntiles : sms;
     auto kern = tridiag_fused_kernel<TI>;
     B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    note_kernel("tridiag_fused_kernel");
     kern<<<grid, VM_COLS + 32, smem, stream>>>(a, m_inf, m_diag, m_sup, m_rhs, S, nTs, tiles_i, ntiles);
     B200_CUDA_CHECK(cudaGetLastError());
     *handled = true;

@@ -239,9 +239,11 @@ extern "C" int b200_vadv(const b200_field *utens_stage, const b200_field *u_stag
         dim3 grid((a.ni + 31) / 32, (a.nj + warps - 1) / warps, 1);
         if (variant == 2) {
             B200_CUDA_CHECK(cudaFuncSetAttribute(vadv_column<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            note_kernel("vadv_column");
             vadv_column<4><<<grid, tpb, smem, stream>>>(a, tpb);
         } else {
             B200_CUDA_CHECK(cudaFuncSetAttribute(vadv_column<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            note_kernel("vadv_column");
             vadv_column<8><<<grid, tpb, smem, stream>>>(a, tpb);
         }
     } else if (variant == 1) {
@@ -254,6 +256,7 @@ extern "C" int b200_vadv(const b200_field *utens_stage, const b200_field *u_stag
             g_scratch_bytes = need;
         }
         dim3 grid((a.ni + 127) / 128, a.nj, 1);
+        note_kernel("vadv_column_gmem");
         vadv_column_gmem<<<grid, 128, 0, stream>>>(a, g_scratch);
     } else {
         set_error("vadv: unknown variant %d", variant);

@@ -409,11 +409,13 @@ static int launch_fused2(const VadvArgs &a, cudaStream_t stream, bool *handled)
         }
         auto kern = vadv_fused2_kernel<TI, FK, true>;
         B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        note_kernel("vadv_fused2_kernel");
         kern<<<grid, VM_THREADS, smem, stream>>>(a, m_us, m_w, m_up, m_ut, m_uts, S, SB, nTs, tiles_i, ntiles,
                                                  pol_stream, pol_keep, pol_bwd, nOn, scratch);
     } else {
         auto kern = vadv_fused2_kernel<TI, FK, false>;
         B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        note_kernel("vadv_fused2_kernel");
         kern<<<grid, VM_THREADS, smem, stream>>>(a, m_us, m_w, m_up, m_ut, m_uts, S, SB, nTs, tiles_i, ntiles,
                                                  pol_stream, pol_keep, pol_bwd, nOn, nullptr);
     }

@@ -280,6 +280,7 @@ static int launch_geom(const VadvArgs &a, cudaStream_t stream, bool *handled)
     const int grid = ntiles < sms ? ntiles : sms;
     auto kern = vadv_tma_kernel<TI, KC, RCP>;
     B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    note_kernel("vadv_tma_kernel");
     kern<<<grid, VT_THREADS, smem, stream>>>(a, m_us, m_w, m_up, m_ut, m_uts, S, SB, tiles_i, ntiles);
     B200_CUDA_CHECK(cudaGetLastError());
     *handled = true;

@@ -569,6 +569,7 @@ static int launch_geom(const VadvArgs &a, cudaStream_t stream, bool *handled)
     const int grid = ntiles < sms ? ntiles : sms;
     auto kern = FUSED ? vadv_fused_kernel<TI, KC> : vadv_tmem_kernel<TI, KC>;
     B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    note_kernel("vadv_tmem_kernel");
     kern<<<grid, VM_THREADS, smem, stream>>>(a, m_us, m_w, m_up, m_ut, m_uts, S, SB, nT, tiles_i, ntiles);
     B200_CUDA_CHECK(cudaGetLastError());
     *handled = true;

@@ -30,16 +30,27 @@ _CT = {"bool": ctypes.c_bool, "int8": ctypes.c_int8, "int16": ctypes.c_int16, "i
        "int64": ctypes.c_int64, "float32": ctypes.c_float, "float64": ctypes.c_double}
 
 
+def cubin_cache_dir() -> str:
+    """Content-addressed cubin store shared by every build of this installation (GT4PY_B200_CUBIN_CACHE overrides):
+    the reference's JIT cache keeps one extension module per stencil id (caching.py:159-342), so ``rebuild=True`` or
+    a new stencil id recompiles identical code; here identical generated source is compiled once."""
+    d = os.environ.get("GT4PY_B200_CUBIN_CACHE") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "cubin_cache")
+    os.makedirs(d, exist_ok=True)
+    return d
+
+
 def compile_cubin(src_path: str) -> str:
-    """nvcc -cubin, cached by source hash next to the source."""
+    """nvcc -cubin for sm_100a, cached by the hash of (source, flags)."""
     with open(src_path, "rb") as fh:
-        digest = hashlib.sha256(fh.read() + " ".join(NVCC_FLAGS).encode()).hexdigest()[:16]
-    out = os.path.splitext(src_path)[0] + f".{digest}.cubin"
+        digest = hashlib.sha256(fh.read() + " ".join(NVCC_FLAGS).encode()).hexdigest()[:24]
+    out = os.path.join(cubin_cache_dir(), f"{digest}.cubin")
     if not os.path.exists(out):
-        cmd = [_build.nvcc(), *NVCC_FLAGS, "-cubin", "-o", out, src_path]
+        tmp = f"{out}.{os.getpid()}.tmp"
+        cmd = [_build.nvcc(), *NVCC_FLAGS, "-cubin", "-o", tmp, src_path]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode:
             raise RuntimeError(f"nvcc failed on generated source {src_path}:\n{r.stderr}")
+        os.replace(tmp, out)
     return out
 
 
@@ -99,10 +110,19 @@ class GeneratedStencil(StencilObject):
             cls._scratch = {}
         return cls._mod
 
-    def _temporaries(self, domain):
-        """Global scratch for the OIR temporaries, cached per domain (owned by the stencil class)."""
+    #: scratch sets (one per (domain, stream)) and TMA descriptors kept per class; the least recently used go first
+    SCRATCH_SETS = 8
+    TMAP_ENTRIES = 256
+
+    def _temporaries(self, domain, stream=None):
+        """Global scratch for the OIR temporaries, owned by the stencil class and cached per (domain, stream): two
+        streams (or a captured graph and a live stream) running the same stencil never share temporaries, and a
+        call with another domain does not free what an earlier capture still points at -- a capture in progress
+        takes references to the buffers it bakes in (stencil_object.Graph keeps them alive for its lifetime).
+        OIR temporaries have no initial-value semantics: plain `empty`, no memset."""
         cls = type(self)
-        hit = cls._scratch.get(domain)
+        key = (tuple(domain), _stream_key(stream))
+        hit = cls._scratch.pop(key, None)
         if hit is None:
             hit = {}
             ni, nj, nk = domain
@@ -110,7 +130,7 @@ class GeneratedStencil(StencilObject):
                 (li, hi), (lj, hj) = t["pad"]
                 shape = [ni + li + hi if t["dims"][0] else 1, nj + lj + hj if t["dims"][1] else 1,
                          nk if t["dims"][2] else 1] + list(t["data_dims"])
-                arr = storage.zeros(shape, np.dtype(t["dtype"]), aligned_index=(li, lj, 0) + (0,) * len(t["data_dims"]),
+                arr = storage.empty(shape, np.dtype(t["dtype"]), aligned_index=(li, lj, 0) + (0,) * len(t["data_dims"]),
                                     dimensions=["I", "J", "K"] + [str(d) for d in range(len(t["data_dims"]))])
                 item = arr.dtype.itemsize
                 strides = [s // item for s in arr.strides]
@@ -119,7 +139,10 @@ class GeneratedStencil(StencilObject):
                         strides[d] = 0
                 origin_ptr = arr.ptr + (li * arr.strides[0] if t["dims"][0] else 0) + (lj * arr.strides[1] if t["dims"][1] else 0)
                 hit[t["name"]] = (arr, origin_ptr, strides)
-            cls._scratch = {domain: hit}  # keep one domain's worth
+            while len(cls._scratch) >= cls.SCRATCH_SETS:
+                cls._scratch.pop(next(iter(cls._scratch)))
+        cls._scratch[key] = hit  # most recently used last
+        _hold_for_capture(hit)
         return hit
 
     def _launch_library(self, lib_plan, domain, fields, params, stream):
@@ -155,6 +178,13 @@ class GeneratedStencil(StencilObject):
                 setattr(a, name, None)
                 continue
             item = np.dtype(spec["dtype"]).itemsize
+            # the launcher trusts nothing the validation may have skipped (validate_args=False, or the memoised
+            # (shapes, origins) key, which like the reference's carries no dtype): the reference's bindings reject a
+            # wrong buffer format at the C++ boundary (gtc_common.py:30-62), so does this
+            if int(f.dtype) != _lib.DTYPE_CODES[np.dtype(spec["dtype"])]:
+                raise TypeError(f"The dtype of field '{name}' does not match the stencil's ('{spec['dtype']}')")
+            if int(f.ndim) != spec["ndim"]:
+                raise ValueError(f"Field '{name}' has {int(f.ndim)} dimensions, the stencil expects {spec['ndim']}")
             # the descriptor's axes are the field's own (masked) axes; the kernel indexes I, J, K, data...
             strides, ptr, pos = [0, 0, 0], f.ptr, 0
             for d in range(3):
@@ -167,7 +197,7 @@ class GeneratedStencil(StencilObject):
             unit = unit and (not spec["dims"][0] or strides[0] == 1) and span < (1 << 31) - (1 << 20)
             setattr(a, name, ptr)
             getattr(a, name + "_s")[:] = strides
-        for name, (arr, origin_ptr, strides) in self._temporaries(tuple(domain)).items():
+        for name, (arr, origin_ptr, strides) in self._temporaries(tuple(domain), stream).items():
             setattr(a, name, origin_ptr)
             getattr(a, name + "_s")[:] = strides
             unit = unit and (strides[0] in (0, 1))
@@ -194,9 +224,11 @@ class GeneratedStencil(StencilObject):
                         dev = storage._Buffer(128)  # the descriptor lives in global memory (256-byte aligned)
                         _lib.check(_lib.lib().b200_memcpy_h2d(c_void_p(dev.ptr), blob, 128, None))
                         hit = (dev, int(shift.value))
-                    if len(cls._tmaps) > 64:
-                        cls._tmaps.clear()
+                    while len(cls._tmaps) >= cls.TMAP_ENTRIES:  # least recently made first; a capture holds its own
+                        cls._tmaps.pop(next(iter(cls._tmaps)))
                     cls._tmaps[key] = hit
+                if hit is not False:
+                    _hold_for_capture(hit[0])
                 kname = extra["kernel"]
                 if hit is False:
                     tma_ok[kname] = False
@@ -235,6 +267,23 @@ class GeneratedStencil(StencilObject):
             cls._last_entry_points.append(k["name"] + sfx)
             _lib.check(_lib.lib().b200_launch(mod.kernels[k["name"] + sfx], (ctypes.c_uint32 * 3)(*grid),
                                               (ctypes.c_uint32 * 3)(*block), smem, sh, argp, 1))
+
+
+def _stream_key(stream):
+    if stream is None:
+        return 0
+    h = _lib.stream_handle(stream)
+    return int(h.value or 0)
+
+
+def _hold_for_capture(obj):
+    """During a CUDA-graph capture the graph being built keeps `obj` (device buffers whose addresses the captured
+    launches carry) alive: stencil_object.Graph collects the list on exit."""
+    from . import stencil_object as so
+
+    refs = getattr(so._tls, "graph_refs", None)
+    if refs is not None:
+        refs.append(obj)
 
 
 # threads of a column-kernel CTA along I x J (a thread per column); tuning hook B200_COLUMN_BLOCK=IxJ

@@ -120,7 +120,7 @@ class ArrayView:
 def as_view(arg, name="<field>") -> ArrayView:
     """Device view of `arg`; the counterpart of storage_utils.asarray(arg, device="gpu")
     (storage/cartesian/utils.py:176-229) without any copy."""
-    if type(arg) is storage.DeviceArray:
+    if isinstance(arg, storage.DeviceArray):
         return ArrayView(arg.ptr, arg.shape, arg.strides, arg.dtype, arg)
     cai = getattr(arg, "__cuda_array_interface__", None)
     if cai is None:
@@ -244,11 +244,15 @@ class StencilObject:
                 return {str(k): v for k, v in origin.items()}
             if origin is None:
                 return {}
-            if isinstance(origin, int):
-                return {"_all_": (0, 0, int(origin))}
-            vals = tuple(int(v) for v in origin)
-            if len(vals) == 3:
-                return {"_all_": vals}
+            if isinstance(origin, (str, bytes)):
+                raise TypeError
+            if hasattr(origin, "__iter__"):  # Index.from_value: any length, integers only (gtc/definitions.py:78-100)
+                vals = list(origin)
+                if not vals or not all(isinstance(v, (int, np.integer)) and not isinstance(v, bool) for v in vals):
+                    raise TypeError
+                return {"_all_": tuple(int(v) for v in vals)}
+            if isinstance(origin, (int, np.integer)):  # Index.from_k: the same value on every axis
+                return {"_all_": (int(origin),) * 3}
         except Exception:
             pass
         raise ValueError("Invalid 'origin' value ({})".format(origin))
@@ -396,7 +400,7 @@ class StencilObject:
                 d = tuple(sorted_dims)
             views[name], dims[name], dims_origins[name] = view, d, _get_origin(arg)
         key = (
-            tuple((n, v.shape, dims_origins.get(n) or (0, 0, 0)) for n, v in views.items() if v is not None),
+            tuple((n, v.shape, v.dtype.str, dims_origins.get(n) or (0, 0, 0)) for n, v in views.items() if v is not None),
             tuple(parameter_args),
             None if domain is None else tuple(domain),
             _freeze_origin(origin),
@@ -547,6 +551,7 @@ class Graph:
         self.stream = stream if stream is not None else _lib.Stream()
         self._exec = None
         self._ctx = None
+        self._refs = []  # device buffers (scratch, TMA descriptors) whose addresses the captured launches carry
 
     def __enter__(self):
         if self._exec is not None:
@@ -555,12 +560,14 @@ class Graph:
         self._ctx.__enter__()
         _lib.check(_lib.lib().b200_graph_begin(_lib.stream_handle(self.stream)))
         _tls.capturing = True
+        _tls.graph_refs = self._refs
         return self
 
     def __exit__(self, exc_type, exc, tb):
         from ctypes import byref, c_void_p
 
         _tls.capturing = False
+        _tls.graph_refs = None
         handle = c_void_p()
         rc = _lib.lib().b200_graph_end(_lib.stream_handle(self.stream), byref(handle))
         self._ctx.__exit__(exc_type, exc, tb)

@@ -139,6 +139,7 @@ class DeviceArray:
     """
 
     __slots__ = ("_buf", "ptr", "shape", "strides", "dtype", "__gt_dims__", "__gt_origin__", "__weakref__")
+    __array_priority__ = 100.0
 
     def __init__(self, buf, ptr, shape, strides, dtype, dims=None, origin=None):
         self._buf = buf
@@ -281,8 +282,8 @@ class DeviceArray:
         buf = _Buffer(max(hi - lo, 1))
         if hi > lo:
             _lib.check(_lib.lib().b200_memcpy_d2d(c_void_p(buf.ptr), c_void_p(self.ptr + lo), hi - lo, None))
-        return DeviceArray(buf, buf.ptr - lo, self.shape, self.strides, self.dtype,
-                           self.__gt_dims__, self.__gt_origin__)
+        return type(self)(buf, buf.ptr - lo, self.shape, self.strides, self.dtype,
+                          self.__gt_dims__, self.__gt_origin__)
 
     # -- views -----------------------------------------------------------------------------------
     def __getitem__(self, key):
@@ -311,7 +312,7 @@ class DeviceArray:
                 strides.append(s * step)
             else:
                 raise TypeError("DeviceArray supports only int / slice / Ellipsis indexing")
-        return DeviceArray(self._buf, ptr, shape, strides, self.dtype)
+        return type(self)(self._buf, ptr, shape, strides, self.dtype)
 
     def __setitem__(self, key, value):
         self[key].set(value.asnumpy() if isinstance(value, DeviceArray) else value)
@@ -321,8 +322,8 @@ class DeviceArray:
             axes = tuple(axes[0])
         if not axes:
             axes = tuple(reversed(range(self.ndim)))
-        return DeviceArray(self._buf, self.ptr, [self.shape[a] for a in axes],
-                           [self.strides[a] for a in axes], self.dtype)
+        return type(self)(self._buf, self.ptr, [self.shape[a] for a in axes],
+                          [self.strides[a] for a in axes], self.dtype)
 
 
 # ---- public interface (interface.py:40-327) ------------------------------------------------------
@@ -332,20 +333,38 @@ def _check_backend(backend):
                            f"(only '{BACKEND_NAME}').")
 
 
-def empty(shape, dtype=np.float64, *, backend: str = BACKEND_NAME,
-          aligned_index: Optional[Sequence[int]] = None,
-          dimensions: Optional[Sequence[str]] = None) -> DeviceArray:
-    _check_backend(backend)
-    aligned_index, shape, dtype, dimensions = normalize_storage_spec(aligned_index, shape, dtype, dimensions)
-    lm = layout_map(dimensions)
+#: class of the arrays the allocators return; a subclass of DeviceArray may be installed (test harnesses that need
+#: numpy-like conveniences on top of the plain device view)
+_ARRAY_CLASS = [None]
+
+
+def set_array_class(cls) -> None:
+    if cls is not None and not issubclass(cls, DeviceArray):
+        raise TypeError("array class must derive from DeviceArray")
+    _ARRAY_CLASS[0] = cls
+
+
+def array_class():
+    return _ARRAY_CLASS[0] or DeviceArray
+
+
+def allocate(shape, lm, dtype, byte_alignment: int, aligned_index) -> "DeviceArray":
+    """The reference's padded / aligned allocation (storage/allocators.py:189-275) over cudaMalloc, for any layout
+    map and alignment: only the contiguous dimension is padded (to whole aligned blocks), and the start is shifted
+    so that `aligned_index` along the contiguous dimension lands on a `byte_alignment` boundary."""
+    dtype = np.dtype(dtype)
     item = dtype.itemsize
     ndim = len(shape)
-    byte_alignment = ALIGNMENT * item
-    dims_layout = [lm.index(i) for i in range(ndim)]  # slowest ... fastest dimension
+    if len(lm) != ndim or sorted(lm) != list(range(ndim)):
+        raise ValueError(f"Invalid layout_map {lm} for shape {shape}")
+    if math.gcd(byte_alignment, item) not in (byte_alignment, item):
+        raise ValueError(f"Incompatible 'byte_alignment' ({byte_alignment}) and 'dtype' size ({item})")
+    per_block = (byte_alignment // item) or 1
+    dims_layout = [list(lm).index(i) for i in range(ndim)]  # slowest ... fastest dimension
     padded = list(shape)
     if ndim:
         c = dims_layout[-1]
-        padded[c] = math.ceil(shape[c] / ALIGNMENT) * ALIGNMENT
+        padded[c] = math.ceil(shape[c] / per_block) * per_block
     total = item * int(np.prod(padded, dtype=np.int64)) + (byte_alignment - 1)
     strides = [item] * ndim
     acc = item
@@ -354,12 +373,20 @@ def empty(shape, dtype=np.float64, *, backend: str = BACKEND_NAME,
     buf = _Buffer(total)
     if ndim:
         c = dims_layout[-1]
-        aligned_off = (ALIGNMENT * math.ceil(aligned_index[c] / ALIGNMENT) - aligned_index[c]) * item
+        aligned_off = (per_block * math.ceil(aligned_index[c] / per_block) - aligned_index[c]) * item
     else:
         aligned_off = 0
     mismatch = (byte_alignment - buf.ptr % byte_alignment) % byte_alignment
     byte_offset = (aligned_off + mismatch) % byte_alignment
-    return DeviceArray(buf, buf.ptr + byte_offset, shape, strides, dtype)
+    return array_class()(buf, buf.ptr + byte_offset, shape, strides, dtype)
+
+
+def empty(shape, dtype=np.float64, *, backend: str = BACKEND_NAME,
+          aligned_index: Optional[Sequence[int]] = None,
+          dimensions: Optional[Sequence[str]] = None) -> DeviceArray:
+    _check_backend(backend)
+    aligned_index, shape, dtype, dimensions = normalize_storage_spec(aligned_index, shape, dtype, dimensions)
+    return allocate(shape, layout_map(dimensions), dtype, ALIGNMENT * dtype.itemsize, aligned_index)
 
 
 def zeros(shape, dtype=np.float64, *, backend: str = BACKEND_NAME, aligned_index=None, dimensions=None):
@@ -436,6 +463,35 @@ def free_pinned(host: np.ndarray) -> None:
     owner = _PINNED_OWNERS.pop(host.ctypes.data, None)
     if owner is not None:
         owner.__del__()
+
+
+def as_device_array(obj) -> DeviceArray:
+    """Device view / copy of `obj` -- what ``cupy.asarray`` is to the reference (storage/cartesian/utils.py:176-213):
+    an object exposing ``__cuda_array_interface__`` is wrapped without a copy (the wrapper keeps it alive), a host
+    array is copied to a fresh allocation with the same element order (C or Fortran)."""
+    if isinstance(obj, DeviceArray):
+        return obj
+    cai = getattr(obj, "__cuda_array_interface__", None)
+    if cai is not None:
+        shape = tuple(int(x) for x in cai["shape"])
+        dtype = np.dtype(cai["typestr"])
+        strides = cai.get("strides")
+        if strides is None:
+            strides, acc = [0] * len(shape), dtype.itemsize
+            for d in range(len(shape) - 1, -1, -1):
+                strides[d] = acc
+                acc *= shape[d]
+        return array_class()(obj, int(cai["data"][0] or 0), shape, strides, dtype,
+                             getattr(obj, "__gt_dims__", None), getattr(obj, "__gt_origin__", None))
+    host = np.asarray(obj)
+    if host.dtype == object:
+        raise TypeError(f"Cannot convert {type(obj)} to a device array")
+    fortran = host.ndim > 1 and host.flags.f_contiguous and not host.flags.c_contiguous
+    host = np.asfortranarray(host) if fortran else np.ascontiguousarray(host)
+    buf = _Buffer(max(host.nbytes, 1))
+    if host.nbytes:
+        _lib.check(_lib.lib().b200_memcpy_h2d(c_void_p(buf.ptr), host.ctypes.data, host.nbytes, None))
+    return array_class()(buf, buf.ptr, host.shape, host.strides, host.dtype)
 
 
 def asnumpy(array) -> np.ndarray:

@@ -73,6 +73,9 @@ typedef struct b200_field {
 /* ---- library / device ------------------------------------------------------------------- */
 B200_API int b200_abi_version(void);
 B200_API const char *b200_last_error(void);
+/* name of the kernel the last b200_hdiff / b200_vadv / b200_tridiag call of this thread launched (what `variant = 0`
+ * resolved to): measurements and tests report what really ran instead of assuming it */
+B200_API const char *b200_last_kernel(void);
 B200_API int b200_device_count(int *count);
 B200_API int b200_set_device(int device);
 B200_API int b200_get_device(int *device);
@@ -94,6 +97,7 @@ B200_API int b200_memcpy2d_h2d(void *dst, size_t dpitch, const void *src, size_t
                       size_t height, void *stream);
 B200_API int b200_memcpy2d_d2h(void *dst, size_t dpitch, const void *src, size_t spitch, size_t width,
                       size_t height, void *stream);
+/* stream == NULL: legacy default stream and complete on return (like the copies); otherwise asynchronous on `stream` */
 B200_API int b200_memset(void *dst, int value, size_t bytes, void *stream);
 
 /* ---- streams / events ------------------------------------------------------------------- */

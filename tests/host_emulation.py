@@ -64,6 +64,7 @@ static unsigned char *emu_map_window(size_t bytes, int mode, void **base, size_t
 """
 
 TILE_LAUNCHER = r"""
+extern "C" {{ int emu_is_tile_{name} = 1; }}
 extern "C" void emu_{name}(const Args *a, unsigned gx, unsigned gy, unsigned gz, unsigned bx, unsigned by, unsigned bz,
                            unsigned smem_bytes, int mode)
 {{
@@ -125,6 +126,12 @@ def _host_source(src: str, plan) -> str:
 
 
 def build(plan_dir: str):
+    plan, lib = build_lib(plan_dir)
+    return plan, ctypes.CDLL(lib)
+
+
+def build_lib(plan_dir: str):
+    """(plan, path of the host shared library made from the plan's kernel.cu); cached by content."""
     with open(os.path.join(plan_dir, "plan.json")) as fh:
         plan = json.load(fh)
     with open(os.path.join(plan_dir, plan.get("source", "kernel.cu"))) as fh:
@@ -146,7 +153,7 @@ def build(plan_dir: str):
             raise RuntimeError(f"g++ failed on the host form of {plan_dir}:\n{r.stderr[:4000]}")
         os.replace(tmp, lib)
         os.remove(cpp)
-    return plan, ctypes.CDLL(lib)
+    return plan, lib
 
 
 def run(plan_dir: str, fields: dict, params: dict, origins: dict, domain, window_mode: int = 0):
