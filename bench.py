@@ -2,29 +2,41 @@
 """bench.py -- the measured hot path: hdiff + vadv on synthetic float64 fields (BASELINE.json).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
-                    [--domain NI NJ NK] [--no-e2e] [--no-cpu-baseline]
+                    [--domain NI NJ NK] [--no-e2e] [--no-cpu-baseline] [--no-configs] [--no-parity]
 
-Workload (config.workload): BASELINE.json configs[2], "hdiff + vadv at 1024x1024x80 float64 on
-1xB200 vs HBM roofline" -- per GPU.  One *step* = one horizontal_diffusion call + one
-vertical_advection_dycore call over one set of fields (2 kernel launches, 2 * NI*NJ*NK grid-point
-updates).  With N > 1 (torchrun, one rank per GPU) every rank owns an NI x NJ x NK block of a
-Px x Py IJ decomposition of a global (Px*NI) x (Py*NJ) x NK domain (weak scaling):
-each step first refreshes the width-2 halo of in_field and the +I halo column of wcon from the
-neighbour ranks over NVLink, then runs the two kernels.
+Workload (config.workload): BASELINE.json configs[4], "hdiff + vadv weak-scaling sweep at 2048x2048x80 per GPU with IJ
+decomposition and halo exchange at 1/2/4/8 B200" -- for every N, N = 1 included.  One *step* = one
+horizontal_diffusion call + one vertical_advection_dycore call over one set of fields (2 kernel launches,
+2 * NI*NJ*NK grid-point updates).  With N > 1 (torchrun, one rank per GPU) every rank owns an NI x NJ x NK block of a
+Px x Py IJ decomposition of a global (Px*NI) x (Py*NJ) x NK domain (weak scaling): each step first
+refreshes the width-2 halo of in_field and the +I halo column of wcon from the neighbour ranks over NVLink.
+The fields are synthetic (b200_fill_synthetic: a counter-based hash of the GLOBAL point index, restated in numpy in
+oracle/inputs.py), so every rank -- and the checker -- can compute any window of the same global field.
 
 Numbers on the JSON line
-  value       grid-point updates/s over all ranks, inputs resident in HBM, CUDA-event timed, max
-              over ranks.  Three field sets are rotated (each field is 671 MB >> 126 MB L2).
-  roofline    dominant kernel (vadv): algorithmic bytes (48 B/point) / its mean
-              launch time from per-launch CUDA events in the same timed region, vs the measured
-              HBM copy bandwidth in MEASURED_PEAKS.json.  `kernels` carries the same for hdiff.
-  e2e         same metric through the public host-buffer API: every step copies that step's inputs
-              from pinned host memory, runs the kernels and copies the results back.
-  cpu_baseline  the oracle's C/OpenMP restatement of the reference (kind "port": the reference's
-              numpy backend cannot travel to the GPU box) on the box's host cores.
+  value        grid-point updates/s over all ranks, inputs resident in HBM, CUDA-event timed, max over ranks.
+  roofline     dominant kernel: algorithmic bytes (vadv 48 B/point, hdiff 24) / its mean launch time
+               from per-launch CUDA events in the same timed region, vs the measured HBM copy bandwidth in
+               MEASURED_PEAKS.json; the kernel NAME is what the library reports it launched (b200_last_kernel).
+  kernels      the same for both kernels of the step.
+  configs      (N = 1) driver-visible timings + rooflines of the other BASELINE configs: [2] hdiff + vadv at
+               1024x1024x80 (the north star's single-GPU target), [3] the FV3-style chain at 512x512x128 (generated
+               fused tile kernel, 32 B/point), [1] vadv 256x256x80, [0] hdiff 128x128x80, and the Thomas solver
+               (a3, 56 B/point) at 1024x1024x80.
+  parity       after the timed region: two steps of a small model whose exchanged fields CHANGE every step (hdiff
+               feeds its own output back, vadv's result becomes the next wcon), every received halo cell poisoned
+               with NaN before each refresh, each rank's block compared bit-for-bit with the single-domain C oracle
+               on strips along its four edges, two corners and an interior patch (oracle/model_parity.py).
+               `halo_parity` (N > 1) is the AND over ranks; a false value makes the run exit non-zero.
+  e2e          same metric through the public host-buffer API (gt4py_b200.HostPipeline) at configs[2]'s size per
+               rank: every step copies that step's inputs from pinned host memory, runs the kernels and copies the
+               results back.
+  cpu_baseline the REFERENCE's own numpy backend (oracle/_ref, staged by oracle/make_ref.py) on a bounded sample of
+               the workload on the box's host cores (kind "reference", 1 core: numpy's elementwise loops are
+               single-threaded); the oracle's C/OpenMP restatement on all cores is reported beside it (`cpu_port`).
 
---impl reference times that CPU port alone (all host threads) on the same workload.
-The oracle is used here ONLY as the CPU baseline; the measured path is the CUDA library.
+--impl reference times the reference numpy backend alone (rank 0 only).
+The oracle / the reference are used here ONLY as checker and CPU baseline; the measured path is the CUDA library.
 """
 from __future__ import annotations
 
@@ -41,26 +53,30 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-ALG_BYTES = {"hdiff": 24, "vadv": 48}  # fp64 bytes per grid point
+ALG_BYTES = {"hdiff": 24, "vadv": 48, "tridiag": 56, "chain": 32}  # fp64 bytes per grid point
 METRIC = "grid-points/s (hdiff+vadv, float64)"
 UNIT = "grid-points/s"
+DEFAULT_DOMAIN = (2048, 2048, 80)   # BASELINE configs[4], per GPU
+CONFIG2_DOMAIN = (1024, 1024, 80)   # BASELINE configs[2]
+CPU_SAMPLE_DOMAIN = (256, 256, 80)  # sub-block of the workload the reference numpy backend is timed on
 
 
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--domain", type=int, nargs=3, default=[1024, 1024, 80],
-                    help="per-GPU compute domain NI NJ NK")
-    ap.add_argument("--sets", type=int, default=3, help="field sets rotated between steps")
+    ap.add_argument("--domain", type=int, nargs=3, default=list(DEFAULT_DOMAIN), help="per-GPU compute domain NI NJ NK")
+    ap.add_argument("--sets", type=int, default=2, help="field sets rotated between steps")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--e2e-chunks", type=int, default=8)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip the `configs` block (N = 1)")
+    ap.add_argument("--no-parity", action="store_true")
     ap.add_argument("--halo-mode", default="push", choices=["push", "pull"],
-                    help="N>1: halo refresh by pushing faces into the neighbours' staging buffers (2 kernels) "
-                         "or by pulling boxes out of the neighbours' fields (1 kernel); both over NVLink peer memory")
+                    help="N>1: halo refresh by pushing faces into the neighbours' staging buffers "
+                         "or by pulling boxes out of the neighbours' fields; both over NVLink peer memory")
     ap.add_argument("--no-overlap", action="store_true",
                     help="N>1: run the halo exchange on the compute stream instead of beside it")
     return ap.parse_args()
@@ -76,23 +92,19 @@ def peaks():
 
 
 def workload_name(dom):
-    tag = " (BASELINE configs[2])" if tuple(dom) == (1024, 1024, 80) else ""
+    tag = {DEFAULT_DOMAIN: " (BASELINE configs[4])", CONFIG2_DOMAIN: " (BASELINE configs[2])"}.get(tuple(dom), "")
     return f"hdiff + vadv at {dom[0]}x{dom[1]}x{dom[2]} float64 per GPU{tag}"
 
 
-# ---- host-side synthetic inputs in the device layout (I contiguous) --------------------------------
-def ifirst(a: np.ndarray) -> np.ndarray:
-    """Same logical (I, J, K) array with I-contiguous strides (layout_map (2, 1, 0))."""
-    return np.ascontiguousarray(a.transpose(2, 1, 0)).transpose(2, 1, 0)
+def decomposition(world):
+    return {1: "1x1", 2: "2x1", 4: "2x2", 8: "4x2"}.get(world, f"{world}x1") + " (IxJ ranks)"
 
 
-def make_host_inputs(dom):
-    from oracle import inputs as gen  # input recipes only (numpy); no oracle arithmetic
-
-    ni, nj, nk = dom
-    h = {k: ifirst(v) for k, v in gen.hdiff_inputs(ni, nj, nk, seed=42).items()}
-    v = {k: (ifirst(a) if k != "dtr_stage" else float(a)) for k, a in gen.vadv_inputs(ni, nj, nk, seed=7).items()}
-    return h, v
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
 
 
 # ---- clocks sampler --------------------------------------------------------------------------------
@@ -150,15 +162,51 @@ class ClockSampler:
                 "samples": len(sm), "window": window, "reasons": sorted(reasons)}
 
 
-# ---- CPU leg (oracle port; the reference's numpy backend cannot travel to the GPU box) ---------------
-def cpu_leg(dom, hin, vin, steps, warmup, budget_s=25.0):
-    """Time the OpenMP C restatement of the reference on host arrays.  Returns (ms_per_step, steps)."""
-    from oracle import cpu as oracle
+# ---- CPU legs (the reference's numpy backend; the oracle's OpenMP port beside it) ----------------------------------
+def host_inputs(dom, goff=(0, 0), gdims=None):
+    """The workload's fields for a block at global offset `goff`, as host arrays in the device layout (I contiguous)."""
+    from oracle import inputs as gen  # input recipes only (numpy); no oracle arithmetic
+
+    ni, nj, nk = dom
+    gdims = gdims or (ni, nj)
+    base = gen.hdiff_base2d(goff[0] - 2, goff[1] - 2, ni + 4, nj + 4, gdims[0], gdims[1])
+    h, v = {}, {}
+    for name in ("in_field", "coeff", "out_field"):
+        seed, lo, hi = gen.SYNTH[name]
+        h[name] = np.asfortranarray(gen.hashed_window(goff[0] - 2, goff[1] - 2, ni + 4, nj + 4, nk, seed, lo, hi,
+                                                      base if name == "in_field" else None))
+    for name in ("utens_stage", "u_stage", "wcon", "u_pos", "utens"):
+        seed, lo, hi = gen.SYNTH[name]
+        v[name] = np.asfortranarray(gen.hashed_window(goff[0], goff[1], ni + 1, nj, nk, seed, lo, hi))
+    return h, v, gen.DTR_STAGE
+
+
+def reference_numpy_leg(steps, warmup, budget_s):
+    """Time the reference's own numpy backend (src/gt4py/cartesian/backend/numpy_backend.py:28-84, staged under
+    oracle/_ref) on CPU_SAMPLE_DOMAIN: hdiff + vadv per step.  Returns (ms_per_step, steps, n_points) or None."""
+    from oracle import ref
+
+    if not ref.activate():
+        return None
+    import warnings
+
+    warnings.filterwarnings("ignore")
+    from cartesian_tests.integration_tests.multi_feature_tests import stencil_definitions as sd
+    from gt4py import storage as gt_storage
+    from gt4py.cartesian import gtscript
+
+    dom = CPU_SAMPLE_DOMAIN
+    hd = gtscript.stencil("numpy", sd.REGISTRY["horizontal_diffusion"], format_source=False)
+    va = gtscript.stencil("numpy", sd.REGISTRY["vertical_advection_dycore"], externals={"BET_M": 0.5, "BET_P": 0.5},
+                          format_source=False)
+    h, v, dtr = host_inputs(dom)
+    hs = {k: gt_storage.from_array(a, backend="numpy", aligned_index=(2, 2, 0)) for k, a in h.items()}
+    vs = {k: gt_storage.from_array(a, backend="numpy") for k, a in v.items()}
 
     def step():
-        oracle.hdiff(hin["in_field"], hin["out_field"], hin["coeff"], origin=(2, 2, 0), domain=dom)
-        oracle.vadv(vin["utens_stage"], vin["u_stage"], vin["wcon"], vin["u_pos"], vin["utens"],
-                    dtr_stage=vin["dtr_stage"], origin=(0, 0, 0), domain=dom)
+        hd(hs["in_field"], hs["out_field"], hs["coeff"], origin=(2, 2, 0), domain=dom, validate_args=False)
+        va(vs["utens_stage"], vs["u_stage"], vs["wcon"], vs["u_pos"], vs["utens"], dtr_stage=np.float64(dtr),
+           origin=(0, 0, 0), domain=dom, validate_args=False)
 
     t = time.perf_counter()
     step()
@@ -169,36 +217,74 @@ def cpu_leg(dom, hin, vin, steps, warmup, budget_s=25.0):
     t0 = time.perf_counter()
     for _ in range(steps):
         step()
-    dt = time.perf_counter() - t0
-    return dt / steps * 1e3, steps
+    return (time.perf_counter() - t0) / steps * 1e3, steps, dom[0] * dom[1] * dom[2]
 
 
-def host_threads():
+def port_leg(dom, steps, budget_s):
+    """The oracle's C/OpenMP restatement on all host threads, same fields.  Returns (ms_per_step, steps)."""
+    from oracle import cpu as oracle
+
+    h, v, dtr = host_inputs(dom)
+
+    def step():
+        oracle.hdiff(h["in_field"], h["out_field"], h["coeff"], origin=(2, 2, 0), domain=dom)
+        oracle.vadv(v["utens_stage"], v["u_stage"], v["wcon"], v["u_pos"], v["utens"], dtr_stage=dtr,
+                    origin=(0, 0, 0), domain=dom)
+
+    t = time.perf_counter()
+    step()
+    one = time.perf_counter() - t
+    steps = max(1, min(steps, int(budget_s / max(one, 1e-9))))
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    return (time.perf_counter() - t0) / steps * 1e3, steps
+
+
+def cpu_baseline_block(steps, warmup, budget_ref, budget_port):
+    cores = host_threads()
+    out = {}
+    ref_leg = None
     try:
-        return len(os.sched_getaffinity(0))
-    except Exception:
-        return os.cpu_count() or 1
+        ref_leg = reference_numpy_leg(steps, warmup, budget_ref)
+    except Exception as exc:  # the reference could not be imported / built: say so, fall back to the port
+        out["reference_error"] = f"{type(exc).__name__}: {exc}"[:300]
+    d = CPU_SAMPLE_DOMAIN
+    os.environ["OMP_NUM_THREADS"] = str(cores)  # torchrun pins it to 1; the port uses every core
+    ms_p, steps_p = port_leg(CONFIG2_DOMAIN, steps, budget_port)
+    n2 = CONFIG2_DOMAIN[0] * CONFIG2_DOMAIN[1] * CONFIG2_DOMAIN[2]
+    port = {"value": 2 * n2 / (ms_p * 1e-3), "unit": UNIT, "cores": cores, "kind": "port", "ms_per_step": ms_p,
+            "steps": steps_p,
+            "sample": f"{steps_p} steps of hdiff + vadv at {CONFIG2_DOMAIN} with the oracle's C/OpenMP restatement "
+                      f"(oracle/stencils.c), {cores} threads"}
+    if ref_leg is None:
+        out.update(port)
+        out["note"] = "reference numpy backend unavailable here (oracle/_ref missing); the port is the baseline"
+        return out, port
+    ms, n_steps, n = ref_leg
+    out.update({"value": 2 * n / (ms * 1e-3), "unit": UNIT, "cores": 1, "kind": "reference", "ms_per_step": ms,
+                "steps": n_steps,
+                "sample": f"{n_steps} steps of hdiff + vadv on a {d[0]}x{d[1]}x{d[2]} block of the workload with the "
+                          f"reference's numpy backend (gt4py 1.1.11 staged under oracle/_ref; numpy {np.__version__}, "
+                          "single-threaded elementwise loops: 1 core)",
+                "host_cores_available": cores})
+    return out, port
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    os.environ["OMP_NUM_THREADS"] = str(host_threads())  # torchrun pins it to 1; the CPU arm uses every core
     dom = tuple(args.domain)
-    n = dom[0] * dom[1] * dom[2]
-    hin, vin = make_host_inputs(dom)
-    ms, steps = cpu_leg(dom, hin, vin, args.steps, args.warmup, budget_s=90.0)
-    value = 2 * n / (ms * 1e-3)
-    cores = host_threads()
-    sample = (f"{steps} full steps of the workload (hdiff {dom} + vadv {dom}), oracle C/OpenMP port of the "
-              f"reference semantics, {cores} threads")
+    cpu, port = cpu_baseline_block(args.steps, args.warmup, budget_ref=90.0, budget_port=15.0)
+    value = cpu["value"]
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
-        "steps": steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": workload_name(dom), "domain_per_gpu": list(dom), "device": "host cpu"},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "steps": cpu.get("steps", args.steps), "warmup": args.warmup, "ms_per_step": cpu["ms_per_step"],
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": workload_name(dom), "domain_per_gpu": list(dom), "device": "host cpu",
+                   "sample_domain": list(CPU_SAMPLE_DOMAIN)},
+        "cpu_baseline": cpu, "cpu_port": port,
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -227,19 +313,47 @@ def bind_near_gpu(index: int):
         return f"unbound ({type(exc).__name__})"
 
 
-def halo_leg(halo, sets, stream, gb, barrier, allmax, reps=50):
+# ---- device fields -----------------------------------------------------------------------------------------------
+def make_device_fields(storage, dom, goff, gdims, stream=None):
+    """One set of the workload's eight fields on the device, filled by b200_fill_synthetic in global coordinates."""
+    from oracle import inputs as gen  # recipes (seeds / ranges) only
+
+    ni, nj, nk = dom
+    base = storage.from_array(gen.hdiff_base2d(goff[0] - 2, goff[1] - 2, ni + 4, nj + 4, gdims[0], gdims[1]),
+                              dimensions=["I", "J"])
+    h, v = {}, {}
+    for name in ("in_field", "coeff", "out_field"):
+        seed, lo, hi = gen.SYNTH[name]
+        h[name] = storage.empty((ni + 4, nj + 4, nk), aligned_index=(2, 2, 0))
+        storage.fill_synthetic(h[name], seed, lo, hi, global_offset=(goff[0] - 2, goff[1] - 2),
+                               base2d=base if name == "in_field" else None, stream=stream)
+    for name in ("utens_stage", "u_stage", "wcon", "u_pos", "utens"):
+        seed, lo, hi = gen.SYNTH[name]
+        v[name] = storage.empty((ni + 1, nj, nk))
+        storage.fill_synthetic(v[name], seed, lo, hi, global_offset=goff, stream=stream)
+    return h, v, base
+
+
+def refill(storage, arr, recipe, goff_arr, base=None):
+    from oracle import inputs as gen
+
+    seed, lo, hi = gen.SYNTH[recipe]
+    storage.fill_synthetic(arr, seed, lo, hi, global_offset=goff_arr, base2d=base)
+
+
+def halo_leg(halo, groups, stream, gb, barrier, allmax, reps=50):
     """The halo exchange alone: `reps` x (wcon refresh + in_field refresh) back to back on one stream, CUDA
     events, max over ranks.  Bytes are what one GPU receives over NVLink per step."""
-    nbytes = halo.bytes_received(0) + halo.bytes_received(1)
+    nbytes = sum(halo.bytes_received(g) for g in groups[0])
     for i in range(5):
-        halo.refresh(2 * (i % sets) + 1, stream)
-        halo.refresh(2 * (i % sets), stream)
+        for g in groups[i % len(groups)]:
+            halo.refresh(g, stream)
     barrier()
     e0, e1 = gb.Event(), gb.Event()
     e0.record(stream)
     for i in range(reps):
-        halo.refresh(2 * (i % sets) + 1, stream)
-        halo.refresh(2 * (i % sets), stream)
+        for g in groups[i % len(groups)]:
+            halo.refresh(g, stream)
     e1.record(stream)
     stream.synchronize()
     us = allmax(e0.elapsed_ms(e1)) * 1e3 / reps
@@ -249,7 +363,58 @@ def halo_leg(halo, sets, stream, gb, barrier, allmax, reps=50):
             "unit": "GB/s", "peak": 900.0, "frac": round(gbs / 900.0, 4),
             "peak_source": "NVLink 5 nominal, per direction per GPU (B200_PROFILING.md; measured peer copy 770 GB/s)",
             "note": "faces of 1.3-2.6 MB and 2.5 KB corners: launch/flag latency, not link bandwidth, bounds it",
-            "launches_counted": (5 + reps) * 2 * halo.launches_per_refresh}
+            "launches_counted": (5 + reps) * len(groups[0]) * halo.launches_per_refresh}
+
+
+# ---- the multi-step parity model (see oracle/model_parity.py) -----------------------------------------------------
+def model_parity(gb, storage, hd, va, hset, vset, base, dom, goff, gdims, halo, pgroups, stream, steps=2):
+    """Run `steps` steps of the evolving model on the device and compare this rank's block with the single-domain
+    oracle on the check windows.  Returns (ok, report)."""
+    from oracle import model_parity as mp
+
+    ni, nj, nk = dom
+    A, B = hset["in_field"], hset["out_field"]
+    P, Q = vset["utens_stage"], vset["wcon"]
+    # initial state: both arrays of each chain hold their recipe everywhere (halo frame / column GI included)
+    refill(storage, A, "in_field", (goff[0] - 2, goff[1] - 2), base)
+    refill(storage, B, "in_field", (goff[0] - 2, goff[1] - 2), base)
+    refill(storage, hset["coeff"], "coeff", (goff[0] - 2, goff[1] - 2))
+    refill(storage, P, "utens_stage", goff)
+    refill(storage, Q, "wcon", goff)
+    gb.synchronize()
+    with gb.use_stream(stream):
+        for t in range(steps):
+            x_in, x_out = (A, B) if t % 2 == 0 else (B, A)
+            u, w = (P, Q) if t % 2 == 0 else (Q, P)
+            if halo is not None:
+                g_in, g_w = pgroups[("in", id(x_in))], pgroups[("w", id(w))]
+                halo.poison(g_in, stream)
+                halo.poison(g_w, stream)
+                halo.refresh(g_w, stream)
+                halo.refresh(g_in, stream)
+            hd(x_in, x_out, hset["coeff"], origin=(2, 2, 0), domain=dom)
+            va(u, vset["u_stage"], w, vset["u_pos"], vset["utens"], dtr_stage=gen_dtr(), origin=(0, 0, 0), domain=dom)
+        stream.synchronize()
+    x_last = B if (steps - 1) % 2 == 0 else A
+    u_last = P if (steps - 1) % 2 == 0 else Q
+    report, ok = {}, True
+    for name, (i0, i1, j0, j1) in mp.windows(goff, dom):
+        want_h = mp.hdiff_chain((i0, i1, j0, j1), steps, gdims, nk)
+        want_v = mp.vadv_chain((i0, i1, j0, j1), steps, gdims, nk)
+        li, lj = i0 - goff[0], j0 - goff[1]
+        got_h = x_last[2 + li:2 + li + (i1 - i0), 2 + lj:2 + lj + (j1 - j0), :].asnumpy()
+        got_v = u_last[li:li + (i1 - i0), lj:lj + (j1 - j0), :].asnumpy()
+        eq_h = bool(np.array_equal(got_h, want_h, equal_nan=True)) and not np.isnan(got_h).any()
+        eq_v = bool(np.array_equal(got_v, want_v, equal_nan=True)) and not np.isnan(got_v).any()
+        report[name] = {"hdiff": eq_h, "vadv": eq_v}
+        ok = ok and eq_h and eq_v
+    return ok, report
+
+
+def gen_dtr():
+    from oracle import inputs as gen
+
+    return gen.DTR_STAGE
 
 
 # ---- the b200 arm ------------------------------------------------------------------------------------
@@ -303,33 +468,54 @@ def run_b200(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    def allmin(x: float) -> float:
+        return -allmax(-x)
+
     dom = tuple(args.domain)
     ni, nj, nk = dom
     n = ni * nj * nk
-    hin, vin = make_host_inputs(dom)
+    from gt4py_b200 import halo as halo_mod
 
-    # device field sets
-    hsets, vsets = [], []
-    for s in range(args.sets):
-        hsets.append({k: storage.from_array(v, aligned_index=(2, 2, 0)) for k, v in hin.items()})
-        vsets.append({k: storage.from_array(v) for k, v in vin.items() if k != "dtr_stage"})
-    dtr = vin["dtr_stage"]
+    decomp = halo_mod.Decomposition.create(world, rank)
+    goff = decomp.global_offset(dom)
+    gdims = (decomp.px_count * ni, decomp.py_count * nj)
+
+    # device field sets (set 0 filled by the synthetic-data kernel, the others are device copies of it)
+    t_setup = time.perf_counter()
+    h0, v0, base = make_device_fields(storage, dom, goff, gdims)
+    hsets, vsets = [h0], [v0]
+    for _ in range(1, max(1, args.sets)):
+        hsets.append({k: a.copy() for k, a in h0.items()})
+        vsets.append({k: a.copy() for k, a in v0.items()})
+    gb.synchronize()
+    setup_s = time.perf_counter() - t_setup
+    dtr = gen_dtr()
 
     hd = stencils.HorizontalDiffusion()
     va = stencils.VerticalAdvectionDycore()
     type(hd).configure(device_sync=False)
     type(va).configure(device_sync=False)
 
-    halo = None
+    halo, groups, pgroups = None, [], {}
     if world > 1:
-        from gt4py_b200 import halo as halo_mod
-
-        halo = halo_mod.HaloExchanger.for_bench(dist, rank, world, local, hsets, vsets, dom, mode=args.halo_mode)
+        halo = halo_mod.HaloExchanger(halo_mod.TorchComm(dist), decomp, mode=args.halo_mode)
+        h_in = halo_mod.halo_from_field_info(hd, "in_field")   # ((2, 2), (2, 2)) from field_info.boundary
+        h_w = halo_mod.halo_from_field_info(va, "wcon")        # ((0, 1), (0, 0))
+        for h, v in zip(hsets, vsets):
+            g_w = halo.add_group([(v["wcon"], (0, 0, 0), dom, h_w)])
+            g_in = halo.add_group([(h["in_field"], (2, 2, 0), dom, h_in)])
+            groups.append((g_w, g_in))
+            pgroups[("w", id(v["wcon"]))], pgroups[("in", id(h["in_field"]))] = g_w, g_in
+        # the parity model swaps array roles: set 0's out_field takes the in-role, its utens_stage the wcon-role
+        pgroups[("in", id(h0["out_field"]))] = halo.add_group([(h0["out_field"], (2, 2, 0), dom, h_in)])
+        pgroups[("w", id(v0["utens_stage"]))] = halo.add_group([(v0["utens_stage"], (0, 0, 0), dom, h_w)])
+        halo.finalize()
 
     stream = gb.Stream()
     overlap = halo is not None and not args.no_overlap
     stream_h = gb.Stream() if overlap else None          # halo exchange runs beside the compute stream
     ev_step, ev_wcon, ev_in = (gb.Event(), gb.Event(), gb.Event()) if overlap else (None, None, None)
+    names = {}
 
     def run_hdiff(h):
         hd(h["in_field"], h["out_field"], h["coeff"], origin=(2, 2, 0), domain=dom)
@@ -343,14 +529,15 @@ def run_b200(args):
         refreshed from the neighbour GPUs first (every rank calls refresh the same number of times).  With
         overlap the exchange runs on its own stream: vadv waits only for wcon's (one column, one neighbour),
         and in_field's (8 neighbours) is hidden behind vadv; ev = (before first, between, after second kernel)."""
-        s = i % args.sets
+        s = i % len(hsets)
         h, v = hsets[s], vsets[s]
         if overlap and refresh:
+            g_w, g_in = groups[s]
             ev_step.record(stream)
             stream_h.wait_event(ev_step)                 # not before the previous users of these fields
-            halo.refresh(2 * s + 1, stream_h)            # wcon
+            halo.refresh(g_w, stream_h)                  # wcon
             ev_wcon.record(stream_h)
-            halo.refresh(2 * s, stream_h)                # in_field
+            halo.refresh(g_in, stream_h)                 # in_field
             ev_in.record(stream_h)
             stream.wait_event(ev_wcon)
             if ev is not None:
@@ -364,8 +551,8 @@ def run_b200(args):
                 ev[2].record(stream)
             return
         if halo is not None and refresh:
-            halo.refresh(2 * s + 1, stream)
-            halo.refresh(2 * s, stream)
+            for g in groups[s]:
+                halo.refresh(g, stream)
         if ev is not None:
             ev[0].record(stream)
         run_hdiff(h)
@@ -377,6 +564,10 @@ def run_b200(args):
 
     sampler = ClockSampler(local) if rank == 0 else None
     with gb.use_stream(stream):
+        run_hdiff(hsets[0])
+        names["hdiff"] = _lib.last_kernel()              # what `variant = 0` resolved to for these fields
+        run_vadv(vsets[0])
+        names["vadv"] = _lib.last_kernel()
         for i in range(max(args.warmup, 3)):
             step(i)
         barrier()
@@ -405,100 +596,251 @@ def run_b200(args):
     t_h, t_v = (t_second, t_first) if overlap else (t_first, t_second)  # overlap runs vadv first
     peak, peak_src = peaks()
 
-    def roof(name, t_ms, kernel):
-        ach = n * ALG_BYTES[name] / (t_ms * 1e-3) / 1e9
+    def roof(name, t_ms, kernel, npts=n):
+        ach = npts * ALG_BYTES[name] / (t_ms * 1e-3) / 1e9
         return {"kernel": kernel, "bound": "hbm", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s",
                 "frac": round(ach / peak, 4), "frac_of_nominal_8TBs": round(ach / 8000.0, 4),
-                "traffic": TRAFFIC.get(name), "ms_per_launch": round(t_ms, 4),
-                "alg_bytes_per_launch": n * ALG_BYTES[name], "peak_source": peak_src}
+                "traffic": traffic_for(kernel, npts), "ms_per_launch": round(t_ms, 4),
+                "alg_bytes_per_launch": npts * ALG_BYTES[name], "peak_source": peak_src}
 
-    kernels = {"hdiff": roof("hdiff", t_h, "hdiff_tma_kernel"), "vadv": roof("vadv", t_v, "vadv_fused2_kernel")}
+    kernels = {"hdiff": roof("hdiff", t_h, names["hdiff"]), "vadv": roof("vadv", t_v, names["vadv"])}
     dominant = "vadv" if t_v >= t_h else "hdiff"
-    halo_line = halo_leg(halo, args.sets, stream, gb, barrier, allmax) if halo is not None else None
+    halo_line = halo_leg(halo, groups, stream, gb, barrier, allmax) if halo is not None else None
+
+    # ---- parity of the step (and of the halo exchange) against the single-domain oracle ----------------
+    parity = None
+    if not args.no_parity:
+        t_p = time.perf_counter()
+        ok, report = model_parity(gb, storage, hd, va, hsets[0], vsets[0], base, dom, goff, gdims, halo, pgroups, stream)
+        all_ok = allmin(1.0 if ok else 0.0) == 1.0
+        parity = {"ok": all_ok, "rank0_windows": report, "steps": 2, "seconds": round(time.perf_counter() - t_p, 2),
+                  "how": "2 model steps with changing exchanged fields, received halo cells poisoned with NaN before "
+                         "each refresh; strips along the 4 block edges, 2 corners and an interior patch of every rank "
+                         "compared bit-for-bit with the single-domain C oracle (oracle/model_parity.py)"}
+
+    # free the big sets before the side legs
+    del evs
+    hsets, vsets = hsets[:1], vsets[:1]
+
+    # ---- the other BASELINE configs (N = 1) -----------------------------------------------------------
+    configs = None
+    if world == 1 and not args.no_configs:
+        configs = run_configs(gb, _lib, storage, stencils, stream, roof, args)
 
     # ---- e2e: host buffers in, host buffers out, every step (public API) ----------------------------
     e2e = None
     if not args.no_e2e:
-        e2e = run_e2e(gb, storage, hd, va, hsets[0], vsets[0], hin, vin, dom, dtr, args, barrier, allmax, world, halo)
+        e2e = run_e2e(gb, storage, hd, va, args, barrier, allmax, world, decomp)
 
     # ---- CPU baseline (rank 0, N == 1 only) ---------------------------------------------------------
-    cpu = None
+    cpu, port = None, None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        ms_cpu, steps_cpu = cpu_leg(dom, hin, vin, args.steps, 2, budget_s=20.0)
-        cores = host_threads()
-        cpu = {"value": 2 * n / (ms_cpu * 1e-3), "unit": UNIT, "cores": cores, "kind": "port",
-               "sample": f"{steps_cpu} full steps of the same workload with the oracle C/OpenMP port "
-                         f"({cores} threads); the reference numpy backend cannot travel to the GPU box",
-               "ms_per_step": ms_cpu}
+        cpu, port = cpu_baseline_block(args.steps, 2, budget_ref=20.0, budget_port=8.0)
 
+    rc = 0
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": workload_name(dom), "domain_per_gpu": list(dom),
+                       "global_domain": [gdims[0], gdims[1], nk],
                        "decomposition": decomposition(world), "field_sets_rotated": args.sets,
-                       "l2_policy": "inputs larger than L2 (671 MB per field, 3 sets rotated); no flush",
+                       "l2_policy": f"inputs larger than L2 ({n * 8 / 1e6:.0f} MB per field, {args.sets} sets rotated); "
+                                    "no flush",
+                       "data_generation": "b200_fill_synthetic on the device (counter-based hash of the global point "
+                                          f"index), {setup_s:.1f} s",
                        "halo_mode": args.halo_mode if world > 1 else None,
                        "halo_overlap": ("exchange on its own stream: wcon's exposed, in_field's hidden behind vadv"
                                         if overlap else None)},
             "effective_GBs": round(value / 2 * (ALG_BYTES["hdiff"] + ALG_BYTES["vadv"]) / 1e9, 1),
             "roofline": kernels[dominant], "kernels": kernels,
-            "e2e": e2e, "cpu_baseline": cpu, "clocks": clocks,
+            "parity": parity, "configs": configs,
+            "e2e": e2e, "cpu_baseline": cpu, "cpu_port": port, "clocks": clocks,
             "gpu_launches": 2 * args.steps + (2 * halo.launches_per_refresh * args.steps if halo else 0),
         }
+        if halo is not None:
+            line["halo_parity"] = None if parity is None else parity["ok"]
         if halo_line is not None:
             line["halo_exchange"] = halo_line
             line["config"]["host_affinity"] = affinity
         os.write(result_fd, (json.dumps(line) + "\n").encode())
+        if parity is not None and not parity["ok"]:
+            sys.stderr.write("bench.py: PARITY FAILED against the single-domain oracle\n")
+            rc = 3
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
-    return 0
+    return rc
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full capture
-# (profiles/): filled in once measured, None until then.
-TRAFFIC = {"hdiff": None, "vadv": None}
-try:
-    with open(os.path.join(ROOT, "profiles", "traffic.json")) as _fh:
-        TRAFFIC.update({k: v for k, v in json.load(_fh).items() if k in TRAFFIC})
-except Exception:
-    pass
+# dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full captures (profiles/):
+# {kernel name: {"bytes": per launch, "points": grid points of the captured launch}}; None until measured.
+def traffic_for(kernel, npts):
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as fh:
+            table = json.load(fh)
+    except Exception:
+        return None
+    e = table.get(kernel)
+    if isinstance(e, dict) and e.get("points") == npts:
+        return e.get("bytes")
+    return None
 
 
-def decomposition(world):
-    return {1: "1x1", 2: "2x1", 4: "2x2", 8: "4x2"}.get(world, f"{world}x1") + " (IxJ ranks)"
+def time_calls(gb, stream, call, reps, warm=3):
+    for _ in range(warm):
+        call()
+    stream.synchronize()
+    e0, e1 = gb.Event(), gb.Event()
+    e0.record(stream)
+    for _ in range(reps):
+        call()
+    e1.record(stream)
+    stream.synchronize()
+    return e0.elapsed_ms(e1) / reps
 
 
-def run_e2e(gb, storage, hd, va, h, v, hin, vin, dom, dtr, args, barrier, allmax, world, halo=None):
+def run_configs(gb, _lib, storage, stencils, stream, roof, args):
+    """Driver-visible lines for the other BASELINE configs (single GPU): CUDA-event timed on `stream`, fields far
+    larger than the L2 where the config's size allows it, each with a parity check against the oracle."""
+    from gt4py_b200 import generated
+    from oracle import chain as chain_oracle
+    from oracle import cpu as oracle
+    from oracle import inputs as gen
+
+    out = {}
+    hd, va, tri = stencils.HorizontalDiffusion(), stencils.VerticalAdvectionDycore(), stencils.TridiagonalSolver()
+    for cls in (type(hd), type(va), type(tri)):
+        cls.configure(device_sync=False)
+    with gb.use_stream(stream):
+        # configs[2]: hdiff + vadv at 1024x1024x80 (north star: >= 75 % of HBM peak on one GPU), 3 sets rotated
+        dom = CONFIG2_DOMAIN
+        npts = dom[0] * dom[1] * dom[2]
+        sets = []
+        h0, v0, _ = make_device_fields(storage, dom, (0, 0), dom[:2], stream)
+        sets.append((h0, v0))
+        for _ in range(2):
+            sets.append(({k: a.copy() for k, a in h0.items()}, {k: a.copy() for k, a in v0.items()}))
+        it = [0]
+
+        def call_h():
+            h = sets[it[0] % 3][0]
+            it[0] += 1
+            hd(h["in_field"], h["out_field"], h["coeff"], origin=(2, 2, 0), domain=dom)
+
+        def call_v():
+            v = sets[it[0] % 3][1]
+            it[0] += 1
+            va(v["utens_stage"], v["u_stage"], v["wcon"], v["u_pos"], v["utens"], dtr_stage=gen.DTR_STAGE,
+               origin=(0, 0, 0), domain=dom)
+
+        t_h = time_calls(gb, stream, call_h, 60)
+        k_h = _lib.last_kernel()
+        t_v = time_calls(gb, stream, call_v, 60)
+        k_v = _lib.last_kernel()
+        out["configs[2] hdiff + vadv 1024x1024x80"] = {
+            "ms_per_step": round(t_h + t_v, 4), "grid_points_per_s": 2 * npts / ((t_h + t_v) * 1e-3),
+            "hdiff": roof("hdiff", t_h, k_h, npts), "vadv": roof("vadv", t_v, k_v, npts),
+            "target": ">= 0.75 of nominal 8 TB/s for both kernels (BASELINE.json north_star)"}
+        # a3: the Thomas solver at the same size (sup / rhs are overwritten: refill not needed for timing)
+        tf = {k: storage.empty(dom) for k in ("inf", "diag", "sup", "rhs", "out")}
+        for k, (seed, lo, hi) in {"inf": (81, -1.0, 1.0), "diag": (82, 3.0, 4.0), "sup": (83, -1.0, 1.0),
+                                  "rhs": (84, -1.0, 1.0), "out": (0, 0.0, 0.0)}.items():
+            storage.fill_synthetic(tf[k], seed, lo, hi, stream=stream)
+        t_t = time_calls(gb, stream, lambda: tri(tf["inf"], tf["diag"], tf["sup"], tf["rhs"], tf["out"], domain=dom), 40)
+        out["a3 tridiagonal_solver 1024x1024x80"] = roof("tridiag", t_t, _lib.last_kernel(), npts)
+        # parity of the solver on a J strip (columns are independent), fresh inputs
+        for k, (seed, lo, hi) in {"sup": (83, -1.0, 1.0), "rhs": (84, -1.0, 1.0)}.items():
+            storage.fill_synthetic(tf[k], seed, lo, hi, stream=stream)
+        tri(tf["inf"], tf["diag"], tf["sup"], tf["rhs"], tf["out"], domain=dom)
+        stream.synchronize()
+        js = slice(500, 504)
+        hostf = {k: np.asfortranarray(gen.hashed_window(0, 500, dom[0], 4, dom[2], *{"inf": (81, -1.0, 1.0),
+                 "diag": (82, 3.0, 4.0), "sup": (83, -1.0, 1.0), "rhs": (84, -1.0, 1.0)}[k])) for k in ("inf", "diag", "sup", "rhs")}
+        hostf["out"] = np.zeros_like(hostf["inf"])
+        oracle.tridiag(hostf["inf"], hostf["diag"], hostf["sup"], hostf["rhs"], hostf["out"], domain=(dom[0], 4, dom[2]))
+        out["a3 tridiagonal_solver 1024x1024x80"]["parity"] = bool(
+            np.array_equal(tf["out"][:, js, :].asnumpy(), hostf["out"]))
+        del tf, sets, h0, v0
+
+        # configs[3]: the FV3-style chain at 512x512x128, one generated fused tile kernel
+        cdom, hgt = (512, 512, 128), chain_oracle.HALO
+        cn = cdom[0] * cdom[1] * cdom[2]
+        st = generated.load_plan(os.path.join(ROOT, "tests", "golden", "generated", "fv3_chain"))
+        type(st).configure(device_sync=False)
+        csets = []
+        for s in range(3):
+            f = {}
+            for name, seed in (("phi", 91), ("u", 92), ("v", 93)):
+                f[name] = storage.empty((cdom[0] + 2 * hgt, cdom[1] + 2 * hgt, cdom[2]), aligned_index=(hgt, hgt, 0))
+                storage.fill_synthetic(f[name], seed + 10 * s, -1.0, 1.5, global_offset=(-hgt, -hgt), stream=stream)
+            f["out"] = storage.zeros(cdom)
+            csets.append(f)
+        org = {"_all_": (hgt, hgt, 0), "out": (0, 0, 0)}
+
+        def call_c():
+            f = csets[it[0] % 3]
+            it[0] += 1
+            st(f["phi"], f["u"], f["v"], f["out"], dt=0.05, alpha=0.03, origin=org, domain=cdom)
+
+        t_c = time_calls(gb, stream, call_c, 40)
+        entry = "+".join(type(st)._last_entry_points)
+        r = roof("chain", t_c, f"generated fv3_chain: {entry}", cn)
+        # parity on two levels (the chain is PARALLEL in K; its horizontal regions need the whole IJ plane)
+        f = csets[0]
+        st(f["phi"], f["u"], f["v"], f["out"], dt=0.05, alpha=0.03, origin=org, domain=cdom)
+        stream.synchronize()
+        lv = [0, cdom[2] - 1]
+        host = {name: gen.hashed_window(-hgt, -hgt, cdom[0] + 2 * hgt, cdom[1] + 2 * hgt, cdom[2], seed, -1.0, 1.5)[:, :, lv]
+                for name, seed in (("phi", 91), ("u", 92), ("v", 93))}
+        want = chain_oracle.fv3_chain(host["phi"], host["u"], host["v"], 0.05, 0.03)
+        r["parity"] = bool(np.array_equal(f["out"].asnumpy()[:, :, lv], want))
+        out["configs[3] fv3_chain 512x512x128"] = r
+        del csets
+
+        # configs[1] / configs[0]: the small single-stencil cases (launch-latency territory; L2 resident)
+        for label, stencil_name, d in (("configs[1] vadv 256x256x80", "vadv", (256, 256, 80)),
+                                       ("configs[0] hdiff 128x128x80", "hdiff", (128, 128, 80))):
+            h1, v1, _ = make_device_fields(storage, d, (0, 0), d[:2], stream)
+            if stencil_name == "vadv":
+                t = time_calls(gb, stream, lambda: va(v1["utens_stage"], v1["u_stage"], v1["wcon"], v1["u_pos"],
+                                                      v1["utens"], dtr_stage=gen.DTR_STAGE, origin=(0, 0, 0), domain=d), 200)
+            else:
+                t = time_calls(gb, stream, lambda: hd(h1["in_field"], h1["out_field"], h1["coeff"], origin=(2, 2, 0),
+                                                      domain=d), 200)
+            r = roof(stencil_name, t, _lib.last_kernel(), d[0] * d[1] * d[2])
+            r["note"] = "fields fit the 126 MB L2: back-to-back calls are served from L2, not HBM"
+            out[label] = r
+    return out
+
+
+def run_e2e(gb, storage, hd, va, args, barrier, allmax, world, decomp):
     """Host buffers -> device -> kernels -> host buffers, all inside the timed region, through the public
-    host-buffer call path (gt4py_b200.HostPipeline: slab-wise H2D / kernel / D2H on three streams)."""
+    host-buffer call path (gt4py_b200.HostPipeline: slab-wise H2D / kernel / D2H on three streams), at
+    configs[2]'s size per rank (the pinned mirrors of configs[4]'s 21.5 GB per rank would not fit 8 ranks' host)."""
+    dom = CONFIG2_DOMAIN
     n = dom[0] * dom[1] * dom[2]
-    pin_h = {k: storage.pinned_like(h[k], hin[k]) for k in h}
-    pin_v = {k: storage.pinned_like(v[k], vin[k]) for k in v}
+    goff = decomp.global_offset(dom)
+    h, v, _ = make_device_fields(storage, dom, goff, (decomp.px_count * dom[0], decomp.py_count * dom[1]))
+    gb.synchronize()
+    pin_h = {k: storage.pinned_like(a) for k, a in h.items()}
+    pin_v = {k: storage.pinned_like(a) for k, a in v.items()}
+    for k, a in h.items():
+        a.copy_to_host(pin_h[k])
+    for k, a in v.items():
+        a.copy_to_host(pin_v[k])
+    gb.synchronize()
     pipe_h = gb.HostPipeline(hd, h, origin=(2, 2, 0), domain=dom, axis="K", chunks=args.e2e_chunks)
     pipe_v = gb.HostPipeline(va, v, origin=(0, 0, 0), domain=dom, axis="J", chunks=args.e2e_chunks)
     h2d = d2h = 0
+    dtr = gen_dtr()
 
     def step():
         nonlocal h2d, d2h
-        if halo is not None:
-            # decomposed run: the halo cells of in_field / wcon come from the neighbour GPUs, which need this
-            # rank's boundary values on the device first
-            h["in_field"].copy_from_host(pin_h["in_field"], pipe_h.s_in)
-            v["wcon"].copy_from_host(pin_v["wcon"], pipe_h.s_in)
-            halo.refresh(1, pipe_h.s_in)   # groups of field set 0: wcon, in_field
-            halo.refresh(0, pipe_h.s_in)
-            pipe_h.s_in.synchronize()
-            pre_h, pre_v = ("in_field",), ("wcon",)
-            extra = pin_h["in_field"].nbytes + pin_v["wcon"].nbytes
-        else:
-            pre_h = pre_v = ()
-            extra = 0
-        a_in, a_out = pipe_h(pin_h, preloaded=pre_h)
-        b_in, b_out = pipe_v(pin_v, preloaded=pre_v, dtr_stage=dtr)
-        h2d, d2h = a_in + b_in + extra, a_out + b_out
+        a_in, a_out = pipe_h(pin_h)
+        b_in, b_out = pipe_v(pin_v, dtr_stage=dtr)
+        h2d, d2h = a_in + b_in, a_out + b_out
 
     steps = max(1, min(args.steps, 10))
     for _ in range(2):
@@ -512,8 +854,13 @@ def run_e2e(gb, storage, hd, va, h, v, hin, vin, dom, dtr, args, barrier, allmax
     barrier()
     for p in list(pin_h.values()) + list(pin_v.values()):
         storage.free_pinned(p)
+    pcie = (h2d + d2h) / (ms * 1e-3) / 1e9
     return {"value": 2 * n * world / (ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
             "d2h_bytes_per_step": int(d2h), "ms_per_step": ms, "steps": steps,
+            "workload": workload_name(dom) + " (host-resident fields; no halo exchange on this leg)",
+            "pcie": {"achieved_GBs_both_directions": round(pcie, 1), "h2d_GBs": round(h2d / (ms * 1e-3) / 1e9, 1),
+                     "peak_note": "PCIe Gen5 x16: ~55-57 GB/s per direction in practice; the H2D direction (5 of 6 "
+                                  "field transfers) is the bound"},
             "path": f"pinned host -> gt4py_b200.HostPipeline ({args.e2e_chunks} slabs: H2D / kernel / D2H on 3 streams) "
                     "-> pinned host; wall clock around the calls, which return with results on the host"}
 

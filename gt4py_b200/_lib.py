@@ -100,6 +100,7 @@ _PROTOTYPES = {
     "b200_memcpy2d_h2d": ([_VP, c_size_t, _VP, c_size_t, c_size_t, c_size_t, _VP], c_int),
     "b200_memcpy2d_d2h": ([_VP, c_size_t, _VP, c_size_t, c_size_t, c_size_t, _VP], c_int),
     "b200_memset": ([_VP, c_int, c_size_t, _VP], c_int),
+    "b200_fill_synthetic": ([POINTER(Field), POINTER(Field), ctypes.c_uint64, c_int64, c_int64, c_double, c_double, _VP], c_int),
     "b200_stream_create": ([POINTER(_VP)], c_int),
     "b200_stream_destroy": ([_VP], c_int),
     "b200_stream_sync": ([_VP], c_int),

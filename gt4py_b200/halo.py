@@ -109,6 +109,15 @@ def halo_boxes(decomp: Decomposition, origin: Sequence[int], domain: Sequence[in
     return boxes
 
 
+def halo_from_field_info(stencil, name: str) -> Tuple[Tuple[int, int], Tuple[int, int]]:
+    """Halo widths ((lo_i, hi_i), (lo_j, hi_j)) a stencil reads around its compute domain for field `name`: the
+    I / J entries of ``field_info[name].boundary`` -- the metadata the reference derives for validation
+    (backend/module_generator.py:80-96) -- so the exchange is generated from the stencil, not typed in by hand."""
+    fi = stencil.field_info[name]
+    b = {ax: fi.boundary[n] for n, ax in enumerate("IJK")}
+    return (tuple(int(x) for x in b["I"]), tuple(int(x) for x in b["J"]))
+
+
 class TorchComm:
     """Adapter over torch.distributed (used only to swap IPC handles and for barriers)."""
 
@@ -277,6 +286,19 @@ class HaloExchanger:
         def dense(extent):
             return (1, extent[0], extent[0] * extent[1])
 
+        # "poison" tables: every halo box this rank receives, overwritten with NaN (checks only: a refresh that does
+        # not deliver a box leaves NaNs behind instead of last step's plausible values)
+        self._nan = self._storage._Buffer(256)
+        nan = (ctypes.c_double * 1)(float("nan"))
+        L.check(lib.b200_memcpy_h2d(c_void_p(self._nan.ptr), ctypes.addressof(nan), 8, None))
+        self._poison = []
+        for group in self._groups:
+            entries = []
+            for f, b, _ in self._boxes_of(me, group):
+                arr = group[f][0]
+                dst = arr.ptr + sum(s * st for s, st in zip(b.dst_start, arr.strides))
+                entries.append(box(self._nan.ptr, (0, 0, 0), dst, [st // arr.dtype.itemsize for st in arr.strides], b.extent))
+            self._poison.append(upload(entries))
         self._tables = []
         for g, group in enumerate(self._groups):
             if self.mode == "pull":
@@ -312,6 +334,13 @@ class HaloExchanger:
             self._tables.append(per_parity)
         L.synchronize()
         self._finalized = True
+
+    def poison(self, group: int, stream=None):
+        """Overwrite every halo cell `refresh(group)` is going to deliver with NaN (parity checks)."""
+        dev, n, blocks = self._poison[group]
+        if n:
+            L = self._lib
+            L.check(L.lib().b200_halo_refresh(c_void_p(dev.ptr), n, blocks, None, 0, None, 0, L.stream_handle(stream)))
 
     def bytes_received(self, group: int) -> int:
         """Bytes this rank's halo cells of `group` receive from its neighbours per refresh."""

@@ -204,9 +204,14 @@ class DeviceArray:
 
     # -- host transfer ---------------------------------------------------------------------------
     def asnumpy(self, stream=None) -> np.ndarray:
-        """Copy to host; the result has the same shape and stride ORDER (a strided view of a copy of
-        the byte extent)."""
+        """Copy to host; the result has the same shape and stride ORDER.  A dense (or nearly dense) view is one
+        copy of its byte extent; a sparse window of a large array (a few rows of every level) is gathered with one
+        pitched copy per index of its slower axes instead of dragging the whole extent over PCIe."""
         lo, hi = self._extent()
+        if self.size and self.ndim >= 2 and (hi - lo) > 4 * self.nbytes and min(self.strides) > 0:
+            gathered = self._gather(stream)
+            if gathered is not None:
+                return gathered
         raw = np.empty(hi - lo, dtype=np.uint8)
         if hi > lo:
             _lib.check(_lib.lib().b200_memcpy_d2h(raw.ctypes.data, c_void_p(self.ptr + lo), hi - lo,
@@ -216,6 +221,26 @@ class DeviceArray:
         base = raw[-lo:] if lo else raw
         return np.ndarray(self.shape, dtype=self.dtype, buffer=base.data if self.size else None,
                           strides=self.strides) if self.size else np.empty(self.shape, self.dtype)
+
+    def _gather(self, stream=None):
+        order = sorted(range(self.ndim), key=lambda d: self.strides[d])  # fastest ... slowest
+        item = self.itemsize
+        if self.strides[order[0]] != item:
+            return None
+        # dense host array with the same axis order
+        dense = np.empty([self.shape[d] for d in reversed(order)], dtype=self.dtype)  # C order: slowest first
+        res = dense.transpose([len(order) - 1 - order.index(d) for d in range(self.ndim)])
+        d0, d1 = order[0], order[1]
+        width, height = self.shape[d0] * item, self.shape[d1]
+        outer = order[2:]
+        lib, sh = _lib.lib(), _lib.stream_handle(stream)
+        for idx in np.ndindex(*[self.shape[d] for d in outer]):
+            src = self.ptr + sum(i * self.strides[d] for i, d in zip(idx, outer))
+            dst = res.ctypes.data + sum(i * res.strides[d] for i, d in zip(idx, outer))
+            _lib.check(lib.b200_memcpy2d_d2h(c_void_p(dst), res.strides[d1], c_void_p(src), self.strides[d1], width, height, sh))
+        if stream is not None:
+            _lib.check(lib.b200_stream_sync(sh))
+        return res
 
     def __array__(self, dtype=None, copy=None):
         a = self.asnumpy()
@@ -492,6 +517,23 @@ def as_device_array(obj) -> DeviceArray:
     if host.nbytes:
         _lib.check(_lib.lib().b200_memcpy_h2d(c_void_p(buf.ptr), host.ctypes.data, host.nbytes, None))
     return array_class()(buf, buf.ptr, host.shape, host.strides, host.dtype)
+
+
+def fill_synthetic(array: DeviceArray, seed: int, lo: float, hi: float, *, global_offset=(0, 0), base2d=None,
+                   stream=None) -> DeviceArray:
+    """Fill a 3-D float64 device array (every element, halo cells included) with counter-based synthetic values in
+    global coordinates: element (i, j, k) gets base2d[i, j] + lo + (hi - lo) * u(global_offset + (i, j), k, seed)
+    (b200_fill_synthetic, csrc/synthetic.cu).  Bench / test plumbing."""
+    from .stencil_object import as_view, make_field_desc
+
+    f = make_field_desc(as_view(array), (0,) * array.ndim)
+    b = None
+    if base2d is not None:
+        b = make_field_desc(as_view(base2d), (0,) * base2d.ndim)
+    _lib.check(_lib.lib().b200_fill_synthetic(byref(f), byref(b) if b is not None else None, int(seed),
+                                              int(global_offset[0]), int(global_offset[1]), float(lo), float(hi),
+                                              _lib.stream_handle(stream)))
+    return array
 
 
 def asnumpy(array) -> np.ndarray:

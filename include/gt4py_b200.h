@@ -100,6 +100,13 @@ B200_API int b200_memcpy2d_d2h(void *dst, size_t dpitch, const void *src, size_t
 /* stream == NULL: legacy default stream and complete on return (like the copies); otherwise asynchronous on `stream` */
 B200_API int b200_memset(void *dst, int value, size_t bytes, void *stream);
 
+/* Synthetic data (bench / test plumbing, csrc/synthetic.cu): fill every element of a 3-D float64 field, halo cells
+ * included, with  base2d(i, j) + lo + (hi - lo) * u(gi0 + i, gj0 + j, k, seed),  u in [0, 1) a counter-based hash of the
+ * GLOBAL coordinates (csrc/synthetic.cuh; numpy restatement oracle/inputs.py:hashed_uniform, bit-identical).
+ * base2d may be NULL. */
+B200_API int b200_fill_synthetic(const b200_field *field, const b200_field *base2d, uint64_t seed, int64_t gi0, int64_t gj0,
+                        double lo, double hi, void *stream);
+
 /* ---- streams / events ------------------------------------------------------------------- */
 B200_API int b200_stream_create(void **stream);
 B200_API int b200_stream_destroy(void *stream);

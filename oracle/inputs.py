@@ -54,3 +54,53 @@ def tridiag_inputs(ni: int, nj: int, nk: int, seed: int = 11, dtype=np.float64):
     }
     f["diag"] = (3.0 + rng.uniform(0.0, 1.0, shape)).astype(dtype)
     return f
+
+
+# ---- counter-based fields in GLOBAL coordinates (bench.py, halo parity) ---------------------------------------------
+# numpy restatement of gt4py_b200/csrc/synthetic.cuh (splitmix64 finaliser over the global point index): the device
+# fills its fields with b200_fill_synthetic, the checker computes any window of the same global field here.
+_M64 = np.uint64(0xFFFFFFFFFFFFFFFF)
+
+
+def hashed_uniform(gi, gj, k, seed: int, lo: float, hi: float) -> np.ndarray:
+    """lo + (hi - lo) * u(gi, gj, k, seed) for broadcastable integer index arrays; u in [0, 1)."""
+    with np.errstate(over="ignore"):
+        off = np.int64(1 << 20)
+        x = (np.uint64(seed)
+             + (np.asarray(gi, dtype=np.int64) + off).astype(np.uint64) * np.uint64(0x9E3779B97F4A7C15)
+             + (np.asarray(gj, dtype=np.int64) + off).astype(np.uint64) * np.uint64(0xC2B2AE3D27D4EB4F)
+             + (np.asarray(k, dtype=np.int64) + off).astype(np.uint64) * np.uint64(0x165667B19E3779F9))
+        x = x ^ (x >> np.uint64(30))
+        x = x * np.uint64(0xBF58476D1CE4E5B9)
+        x = x ^ (x >> np.uint64(27))
+        x = x * np.uint64(0x94D049BB133111EB)
+        x = x ^ (x >> np.uint64(31))
+    u = (x >> np.uint64(11)).astype(np.float64) * (1.0 / 9007199254740992.0)
+    t = np.float64(hi - lo) * u
+    return np.float64(lo) + t
+
+
+def hashed_window(gi0: int, gj0: int, ni: int, nj: int, nk: int, seed: int, lo: float, hi: float, base2d=None):
+    """(ni, nj, nk) window of the global field starting at global index (gi0, gj0), level 0."""
+    gi = (gi0 + np.arange(ni, dtype=np.int64))[:, None, None]
+    gj = (gj0 + np.arange(nj, dtype=np.int64))[None, :, None]
+    k = np.arange(nk, dtype=np.int64)[None, None, :]
+    v = hashed_uniform(gi, gj, k, seed, lo, hi)
+    return v if base2d is None else base2d[:, :, None] + v
+
+
+def hdiff_base2d(gi0: int, gj0: int, ni: int, nj: int, gni: int, gnj: int) -> np.ndarray:
+    """The analytic field of the reference's hdiff notebook (demo_horizontal_diffusion.ipynb cell 9) over a window of
+    a gni x gnj global domain: 5 + 8 (2 + cos(pi (x + 1.5 y)) + sin(2 pi (x + 1.5 y))) / 4,  x = gi / gni, y = gj / gnj.
+    Computed on the host (numpy) by both sides -- the device only adds the hashed noise -- so libm never differs."""
+    x = (gi0 + np.arange(ni, dtype=np.float64)) / max(gni, 1)
+    y = (gj0 + np.arange(nj, dtype=np.float64)) / max(gnj, 1)
+    xy = x[:, None] + 1.5 * y[None, :]
+    return 5.0 + 8.0 * (2.0 + np.cos(np.pi * xy) + np.sin(2.0 * np.pi * xy)) / 4.0
+
+
+#: (seed, lo, hi) of every synthetic field of the bench workload
+SYNTH = {"in_field": (42, -0.02, 0.02), "coeff": (0, 0.025, 0.025), "out_field": (0, 0.0, 0.0),
+         "utens_stage": (71, -1.0, 1.0), "u_stage": (72, -1.0, 1.0), "u_pos": (73, -1.0, 1.0), "utens": (74, -1.0, 1.0),
+         "wcon": (75, -0.1, 0.1)}
+DTR_STAGE = 3.0 / 20.0

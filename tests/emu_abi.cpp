@@ -21,6 +21,7 @@
 #include <vector>
 
 #include "../include/gt4py_b200.h"
+#include "../gt4py_b200/csrc/synthetic.cuh"
 
 namespace {
 thread_local char g_err[512] = "";
@@ -86,6 +87,19 @@ int b200_memcpy2d_h2d(void *d, size_t dp, const void *s, size_t sp, size_t w, si
 int b200_memcpy2d_d2h(void *d, size_t dp, const void *s, size_t sp, size_t w, size_t h, void *) { return copy2d(d, dp, s, sp, w, h); }
 int b200_memset(void *dst, int value, size_t bytes, void *) { if (bytes) memset(dst, value, bytes); return B200_OK; }
 
+int b200_fill_synthetic(const b200_field *f, const b200_field *base, uint64_t seed, int64_t gi0, int64_t gj0, double lo,
+                        double hi, void *)
+{
+    double *p = (double *)f->ptr;
+    for (int64_t k = 0; k < f->shape[2]; ++k)
+        for (int64_t j = 0; j < f->shape[1]; ++j)
+            for (int64_t i = 0; i < f->shape[0]; ++i) {
+                const double v = b200::synth_value(gi0 + i, gj0 + j, k, seed, lo, hi);
+                const double b = base ? ((const double *)base->ptr)[i * base->stride[0] + j * base->stride[1]] : 0.0;
+                p[i * f->stride[0] + j * f->stride[1] + k * f->stride[2]] = base ? b + v : v;
+            }
+    return B200_OK;
+}
 int b200_stream_create(void **stream) { *stream = malloc(8); return B200_OK; }
 int b200_stream_destroy(void *stream) { free(stream); return B200_OK; }
 int b200_stream_sync(void *) { return B200_OK; }

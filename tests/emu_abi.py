@@ -22,14 +22,14 @@ ROOT = os.path.dirname(HERE)
 
 def build() -> str:
     src = os.path.join(HERE, "emu_abi.cpp")
-    with open(src, "rb") as fh, open(os.path.join(ROOT, "include", "gt4py_b200.h"), "rb") as hh:
-        tag = hashlib.sha256(fh.read() + hh.read()).hexdigest()[:16]
+    deps = [src, os.path.join(ROOT, "include", "gt4py_b200.h"), os.path.join(ROOT, "gt4py_b200", "csrc", "synthetic.cuh")]
+    tag = hashlib.sha256(b"".join(open(d, "rb").read() for d in deps)).hexdigest()[:16]
     cache = os.path.join(tempfile.gettempdir(), "gt4py_b200_host_emulation")
     os.makedirs(cache, exist_ok=True)
     lib = os.path.join(cache, f"libgt4py_b200_emu_{tag}.so")
     if not os.path.exists(lib):
         tmp = f"{lib}.{os.getpid()}.tmp"
-        subprocess.run(["g++", "-std=c++17", "-O1", "-shared", "-fPIC", "-w", src, "-o", tmp, "-ldl"], check=True)
+        subprocess.run(["g++", "-std=c++17", "-O1", "-ffp-contract=off", "-shared", "-fPIC", "-w", src, "-o", tmp, "-ldl"], check=True)
         os.replace(tmp, lib)
     return lib
 
