@@ -117,6 +117,7 @@ _PROTOTYPES = {
     "b200_stream_wait_event": ([_VP, _VP], c_int),
     "b200_hdiff": ([POINTER(Field), POINTER(Field), POINTER(Field), POINTER(c_int64), c_int, c_int, _VP], c_int),
     "b200_vadv": ([POINTER(Field)] * 5 + [c_double, POINTER(c_int64), c_int, _VP], c_int),
+    "b200_vadv_noalloc": ([POINTER(Field)] * 5 + [c_double, POINTER(c_int64), _VP], c_int),
     "b200_tridiag": ([POINTER(Field)] * 5 + [POINTER(c_int64), c_int, _VP], c_int),
     "b200_ipc_get_mem_handle": ([_VP, _VP], c_int),
     "b200_ipc_open_mem_handle": ([_VP, POINTER(_VP)], c_int),

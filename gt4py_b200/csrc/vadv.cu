@@ -159,7 +159,72 @@ __global__ void __launch_bounds__(128) vadv_column_gmem(VadvArgs a, double *scra
 static double *g_scratch = nullptr;
 static size_t g_scratch_bytes = 0;
 
+// ---- b200_vadv_noalloc: the same kernel with its LIFO in a fixed device array (no allocation, ever) -------------
+// File-scope scratch: B200_VADV_NOALLOC_MAX_POINTS x (ccol, dcol) = 32 MiB, held by every GPU that loads the
+// library until the process exits.  In HOST code the name `g_noalloc_scratch` is only a stand-in for the symbol, not
+// a device address: the address comes from cudaGetSymbolAddress, once per device, with that device current.
+// Nothing in it has to start at zero: the FORWARD sweep stores slot (k, column) before the BACKWARD sweep of the
+// same thread reads it, so the previous call's contents are never observed.
+static __device__ __align__(256) double g_noalloc_scratch[2 * B200_VADV_NOALLOC_MAX_POINTS];
+constexpr int NOALLOC_MAX_DEVICES = 64;
+static double *g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};  // device address of the array, per device ordinal
+
+static int noalloc_scratch(double **out)
+{
+    int dev = 0;
+    B200_CUDA_CHECK(cudaGetDevice(&dev));
+    B200_REQUIRE(dev >= 0 && dev < NOALLOC_MAX_DEVICES, "vadv_noalloc: device ordinal %d out of range", dev);
+    double *p = __atomic_load_n(&g_noalloc_ptr[dev], __ATOMIC_ACQUIRE);
+    if (!p) {  // set-up, once per device (a race between two threads resolves to the same address)
+        void *sym = nullptr;
+        B200_CUDA_CHECK(cudaGetSymbolAddress(&sym, g_noalloc_scratch));
+        B200_REQUIRE(sym != nullptr, "vadv_noalloc: cudaGetSymbolAddress returned a null address");
+        p = static_cast<double *>(sym);
+        __atomic_store_n(&g_noalloc_ptr[dev], p, __ATOMIC_RELEASE);
+    }
+    *out = p;
+    return B200_OK;
+}
+
 }  // namespace b200
+
+extern "C" int b200_vadv_noalloc(const b200_field *utens_stage, const b200_field *u_stage, const b200_field *wcon,
+                                 const b200_field *u_pos, const b200_field *utens, double dtr_stage,
+                                 const int64_t domain[3], void *stream_)
+{
+    using namespace b200;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    B200_REQUIRE(domain, "domain is null");
+    B200_REQUIRE(domain[0] >= 0 && domain[1] >= 0 && domain[2] >= 0, "negative domain");
+    B200_REQUIRE(domain[0] < (1 << 30) && domain[1] < (1 << 30) && domain[2] < (1 << 30), "domain too large");
+    if (domain[0] == 0 || domain[1] == 0 || domain[2] == 0) return B200_OK;
+    B200_REQUIRE(domain[2] >= 3, "vadv needs at least 3 vertical levels (got %lld)", (long long)domain[2]);
+    const long long points = (long long)domain[0] * domain[1] * domain[2];
+    B200_REQUIRE(points <= (long long)B200_VADV_NOALLOC_MAX_POINTS,
+                 "vadv_noalloc: domain %lld x %lld x %lld = %lld grid points exceeds the fixed scratch of %lld points "
+                 "(B200_VADV_NOALLOC_MAX_POINTS); use b200_vadv for larger domains",
+                 (long long)domain[0], (long long)domain[1], (long long)domain[2], points,
+                 (long long)B200_VADV_NOALLOC_MAX_POINTS);
+    const int h0[3] = {0, 0, 0}, hw[3] = {1, 0, 0};
+    VadvArgs a;
+    int rc;
+    if ((rc = make_view<double>(utens_stage, "utens_stage", B200_FLOAT64, domain, h0, h0, &a.utens_stage))) return rc;
+    if ((rc = make_view<const double>(u_stage, "u_stage", B200_FLOAT64, domain, h0, h0, &a.u_stage))) return rc;
+    if ((rc = make_view<const double>(wcon, "wcon", B200_FLOAT64, domain, h0, hw, &a.wcon))) return rc;
+    if ((rc = make_view<const double>(u_pos, "u_pos", B200_FLOAT64, domain, h0, h0, &a.u_pos))) return rc;
+    if ((rc = make_view<const double>(utens, "utens", B200_FLOAT64, domain, h0, h0, &a.utens))) return rc;
+    a.dtr_stage = dtr_stage;
+    a.ni = (int)domain[0];
+    a.nj = (int)domain[1];
+    a.nk = (int)domain[2];
+    double *scratch = nullptr;
+    if ((rc = noalloc_scratch(&scratch))) return rc;
+    dim3 grid((a.ni + 127) / 128, a.nj, 1);
+    note_kernel("vadv_column_gmem");
+    vadv_column_gmem<<<grid, 128, 0, stream>>>(a, scratch);
+    B200_CUDA_CHECK(cudaGetLastError());
+    return B200_OK;
+}
 
 extern "C" int b200_vadv(const b200_field *utens_stage, const b200_field *u_stage,
                          const b200_field *wcon, const b200_field *u_pos, const b200_field *utens,

@@ -149,6 +149,23 @@ B200_API int b200_vadv(const b200_field *utens_stage, const b200_field *u_stage,
               const b200_field *u_pos, const b200_field *utens, double dtr_stage,
               const int64_t domain[3], int variant, void *stream);
 
+/* b200_vadv_noalloc: vertical_advection_dycore for callers that must not allocate.  NO COUNTERPART IN THE REFERENCE:
+ * added (code under CUDA-graph capture, tight serving loops and harnesses
+ * that forbid cudaMalloc).  Same arguments, checks and results (bit-identical) as b200_vadv with variant 1 -- the
+ * thread-per-column kernel whose (ccol, dcol) LIFO lives in global scratch -- but the scratch is a fixed
+ * `static __device__` array inside the library instead of a cudaMalloc'd buffer: the call performs no cudaMalloc,
+ * cudaFree or any other allocating routine.
+ *   limit   domain[0] * domain[1] * domain[2] <= B200_VADV_NOALLOC_MAX_POINTS (2 Mi grid points, e.g. 128 x 128 x 128
+ *           or 160 x 160 x 80; 16 bytes of scratch per point = 32 MiB, resident on every GPU that loads the library
+ *           until the process exits).  Larger domains are rejected with B200_EINVAL and a message; any strides work.
+ *   sharing every call on a device uses the SAME array.  Nothing in it needs clearing (each slot is written by the
+ *           forward sweep before the backward sweep reads it), but calls that overlap on the GPU -- different
+ *           streams, or graph branches without an edge between them -- race on it: serialise them. */
+#define B200_VADV_NOALLOC_MAX_POINTS (2 * 1024 * 1024)
+B200_API int b200_vadv_noalloc(const b200_field *utens_stage, const b200_field *u_stage, const b200_field *wcon,
+                      const b200_field *u_pos, const b200_field *utens, double dtr_stage,
+                      const int64_t domain[3], void *stream);
+
 /* tridiagonal_solver(inf, diag, sup, rhs, out): stencil_definitions.py:219-232 (sup, rhs updated
  * in place). */
 B200_API int b200_tridiag(const b200_field *inf, const b200_field *diag, const b200_field *sup,

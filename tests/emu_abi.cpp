@@ -118,6 +118,8 @@ int b200_graph_destroy(void *) { return B200_OK; }
 int b200_hdiff(const b200_field *, const b200_field *, const b200_field *, const int64_t[3], int, int, void *) { UNSUP("b200_hdiff"); }
 int b200_vadv(const b200_field *, const b200_field *, const b200_field *, const b200_field *, const b200_field *, double,
               const int64_t[3], int, void *) { UNSUP("b200_vadv"); }
+int b200_vadv_noalloc(const b200_field *, const b200_field *, const b200_field *, const b200_field *, const b200_field *,
+                      double, const int64_t[3], void *) { UNSUP("b200_vadv_noalloc"); }
 int b200_tridiag(const b200_field *, const b200_field *, const b200_field *, const b200_field *, const b200_field *,
                  const int64_t[3], int, void *) { UNSUP("b200_tridiag"); }
 
