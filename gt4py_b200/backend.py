@@ -108,6 +108,7 @@ class B200Backend(BaseBackend):
         "use_library_kernels": {"versioning": True, "type": bool},
         "fuse_temporaries": {"versioning": True, "type": bool},
         "k_register_cache": {"versioning": True, "type": bool},
+        "fuse_columns": {"versioning": True, "type": bool},
     }
     storage_info: ClassVar[layout.LayoutInfo] = {
         "alignment": storage.ALIGNMENT,
@@ -153,7 +154,8 @@ class B200Backend(BaseBackend):
         gt4py_b200/library_kernels.json (made by tools/make_library_fingerprints.py)."""
         if not self.builder.options.backend_opts.get("use_library_kernels", True):
             return None
-        raw_plan, _ = lowering.lower(GTIRToOIR().visit(self.builder.gtir), self.builder.options.name, fuse=False)
+        raw_plan, _ = lowering.lower(GTIRToOIR().visit(self.builder.gtir), self.builder.options.name, fuse=False,
+                                     fuse_columns=False)
         fp = raw_plan["fingerprint"]
         entry = library_table().get(fp["digest"])
         if entry is None:
@@ -164,13 +166,14 @@ class B200Backend(BaseBackend):
     def make_plan(self):
         name, fuse = self.builder.options.name, self.fuse
         kc = bool(self.builder.options.backend_opts.get("k_register_cache", False))
+        fc = bool(self.builder.options.backend_opts.get("fuse_columns", True))
         if fuse is None or fuse:
-            plan, source = lowering.lower(self.oir(True), name, fuse=True, k_register_cache=kc)
+            plan, source = lowering.lower(self.oir(True), name, fuse=True, k_register_cache=kc, fuse_columns=fc)
             deepest = max([k.get("stages", 0) for k in plan["kernels"]], default=0)
             if fuse is None and deepest < self.AUTO_FUSE_MIN_STAGES:
                 fuse = False
         if fuse is not None and not fuse:
-            plan, source = lowering.lower(self.oir(False), name, fuse=False, k_register_cache=kc)
+            plan, source = lowering.lower(self.oir(False), name, fuse=False, k_register_cache=kc, fuse_columns=fc)
         match = self.library_match()
         if match is not None:
             plan["library"] = match

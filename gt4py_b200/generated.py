@@ -81,6 +81,10 @@ def _args_struct(plan):
             fields.append((name, c_void_p))  # device address of a CUtensorMap
         elif kind == "origin":
             fields.append((name, ctypes.c_int32 * 3))
+        elif kind == "cf_spill":
+            fields.append((name, c_void_p))
+        elif kind == "cf_smem":
+            fields.append((name, ctypes.c_int32))
         else:
             fields.append((name, _CT[dtype]))
     fields += [("ni", ctypes.c_int32), ("nj", ctypes.c_int32), ("nk", ctypes.c_int32)]
@@ -101,6 +105,9 @@ class GeneratedStencil(StencilObject):
             names = [k["name"] + sfx for k in cls._plan_["kernels"] for sfx in ("", "_u") + (("_t",) if "tma" in k else ())]
             cls._mod = _Module(cubin, names)
             for k in cls._plan_["kernels"]:
+                if k["kind"] == "colfuse":
+                    for sfx in ("", "_u"):
+                        _lib.check(_lib.lib().b200_kernel_set_smem(cls._mod.kernels[k["name"] + sfx], _COLFUSE_SMEM))
                 for sfx, nbytes in (("", k.get("smem_bytes", 0)), ("_u", k.get("smem_bytes", 0)),
                                     ("_t", k.get("tma", {}).get("smem_bytes", 0))):
                     if nbytes > 48 * 1024:  # opt in to more than the default dynamic shared memory
@@ -144,6 +151,17 @@ class GeneratedStencil(StencilObject):
         cls._scratch[key] = hit  # most recently used last
         _hold_for_capture(hit)
         return hit
+
+    def _cf_spill(self, kname, nbytes, stream):
+        """Spill area of a fused column kernel's value stack (per stream; grown on demand, never shrunk)."""
+        cls = type(self)
+        key = ("cf_spill", kname, _stream_key(stream))
+        buf = cls._scratch.get(key)
+        if buf is None or buf.nbytes < max(nbytes, 256):
+            buf = storage._Buffer(max(nbytes, 256))
+            cls._scratch[key] = buf
+        _hold_for_capture(buf)
+        return buf.ptr
 
     def _launch_library(self, lib_plan, domain, fields, params, stream):
         """The stencil was recognised as one the library has a hand-written kernel for (backend.library_match)."""
@@ -259,14 +277,38 @@ class GeneratedStencil(StencilObject):
                 block, grid, smem = (*k["block"], 1), ((ni + ti - 1) // ti, (nj + tj - 1) // tj, nk), k["smem_bytes"]
                 if tma_ok.get(k["name"]):
                     sfx, smem = "_t", k["tma"]["smem_bytes"]
+            elif k["kind"] == "colfuse":
+                # persistent fused FORWARD / BACKWARD kernel (lowering_colfuse.py): a CTA per SM walks 256-column tiles;
+                # the value stack beyond Tensor Memory goes to shared memory, then to an L2-resident spill area
+                bx, by = k["block"]
+                ntiles = ((wi + bx - 1) // bx) * ((wj + by - 1) // by)
+                ctas = max(1, min(ntiles, _sm_count()))
+                need = max(0, nk * k["stack_values_per_level"] - 128)
+                ring = k["ring_slots"] * 2048
+                n_smem = max(0, min(need, (_COLFUSE_SMEM - ring) // 2048))
+                smem = ring + n_smem * 2048
+                spill = self._cf_spill(k["name"], (need - n_smem) * ctas * bx * by * 8, stream)
+                setattr(a, f"cf_{k['name']}_smem", n_smem)
+                setattr(a, f"cf_{k['name']}_spill", spill)
+                block, grid = (bx, by, 1), (ctas, 1, 1)
             else:
                 bx, by = _COLUMN_BLOCK
                 block, grid = (bx, by, 1), ((wi + bx - 1) // bx, (wj + by - 1) // by, 1)
-            if nk <= 0 and k["kind"] != "column":
+            if nk <= 0 and k["kind"] not in ("column", "colfuse"):
                 continue
             cls._last_entry_points.append(k["name"] + sfx)
             _lib.check(_lib.lib().b200_launch(mod.kernels[k["name"] + sfx], (ctypes.c_uint32 * 3)(*grid),
                                               (ctypes.c_uint32 * 3)(*block), smem, sh, argp, 1))
+
+
+_COLFUSE_SMEM = 226 * 1024  # dynamic shared memory a fused column kernel may use (227 KB minus its static part)
+_SM_COUNT = []
+
+
+def _sm_count() -> int:
+    if not _SM_COUNT:
+        _SM_COUNT.append(int(_lib.device_props()["sm_count"]))
+    return _SM_COUNT[0]
 
 
 def _stream_key(stream):

@@ -1,0 +1,426 @@
+"""Fused FORWARD / BACKWARD column kernels -- the generic form of csrc/vadv_fused.cu's machine mapping.
+
+A run of consecutive sequential vertical loops whose cross-loop dependencies stay inside a column (vadv: Thomas
+forward elimination + back substitution; the tridiagonal solver; column physics) is lowered to ONE persistent
+kernel instead of one thread-per-column kernel per loop with the intermediate fields in HBM:
+
+* a CTA of 256 threads walks 256-column tiles; a thread owns a column and runs all loops of the run on it;
+* fields that carry values from level to level and from loop to loop -- the ones the reference's pipeline
+  annotates ``KCache(fill, flush)`` (gtc/oir.py:310-320, passes/oir_optimizations/caches.py:44-253; GridTools
+  realises them as ring buffers, gtcpp_codegen.py:227-232) -- live in registers (current and previous level) and,
+  between loops, on a per-thread VALUE STACK: Tensor Memory for the first 128 values of a thread, shared memory
+  next, an L2-resident scratch beyond (helpers in lowering.PRELUDE).  Temporaries that never leave the run cost no
+  DRAM byte; API fields written in one loop and read in the next are stored once and never re-read;
+* read-only inputs are prefetched `LEAD` levels ahead by cp.async into a per-thread shared-memory ring (a thread
+  reads only what it copied itself: no barrier), which replaces occupancy as the latency-hiding mechanism -- with
+  ~256 columns per SM in flight the stack stays on chip.
+
+Semantics are those of the column kernels of lowering.py (sections in program order, one level at a time).
+"""
+from __future__ import annotations
+
+import os
+from typing import Any, Dict, List, Set, Tuple
+
+from gt4py.cartesian.gtc import common, oir
+
+BX, BY = 128, 2          # threads of a CTA along I x J (one column each)
+LEAD = int(os.environ.get("B200_COLFUSE_LEAD", "6"))  # levels the prefetch runs ahead
+
+
+def _walk(stmts, cond=False, restricted=False):
+    """(kind, FieldAccess, conditional, restricted) in evaluation order; kind 'r' / 'w'."""
+    for st in stmts:
+        if isinstance(st, oir.AssignStmt):
+            for n in st.right.walk_values():
+                if isinstance(n, oir.FieldAccess):
+                    yield "r", n, cond, restricted
+            if isinstance(st.left, oir.FieldAccess):
+                subs = list(st.left.data_index)
+                if isinstance(st.left.offset, oir.VariableKOffset):
+                    subs.append(st.left.offset.k)
+                for sub in subs:
+                    for n in sub.walk_values():
+                        if isinstance(n, oir.FieldAccess):
+                            yield "r", n, cond, restricted
+                yield "w", st.left, cond, restricted
+        elif isinstance(st, oir.MaskStmt):
+            for n in st.mask.walk_values():
+                if isinstance(n, oir.FieldAccess):
+                    yield "r", n, cond, restricted
+            yield from _walk(st.body, True, restricted)
+        elif isinstance(st, oir.While):
+            for n in st.cond.walk_values():
+                if isinstance(n, oir.FieldAccess):
+                    yield "r", n, True, restricted
+            yield from _walk(st.body, True, restricted)
+        elif isinstance(st, oir.HorizontalRestriction):
+            yield from _walk(st.body, True, True)
+        elif hasattr(st, "body"):
+            yield from _walk(st.body, cond, restricted)
+
+
+def _sections(unit):
+    """[(interval, [hexec, ...])] in program order."""
+    out = []
+    for interval, h in unit:
+        if out and out[-1][0] is interval:
+            out[-1][1].append(h)
+        else:
+            out.append((interval, [h]))
+    return out
+
+
+def _same_bound(a: common.AxisBound, b: common.AxisBound) -> bool:
+    return a.level == b.level and int(a.offset) == int(b.offset)
+
+
+def _contiguous(sections, backward: bool) -> bool:
+    for (a, _), (b, _) in zip(sections, sections[1:]):
+        if backward and not _same_bound(b.end, a.start):
+            return False
+        if not backward and not _same_bound(a.end, b.start):
+            return False
+    return True
+
+
+def find_runs(stencil: oir.Stencil, units_by_loop) -> List[List[int]]:
+    """Maximal runs (>= 2 loops) of consecutive sequential vertical loops that can share one kernel: every loop is a
+    single column kernel, its sections tile a contiguous K range in order, and every field written inside the run is
+    only ever touched at horizontal offset (0, 0) inside the run."""
+    ok = []
+    for n_loop, loop, units in units_by_loop:
+        seq = loop.loop_order != common.LoopOrder.PARALLEL
+        good = seq and len(units) == 1 and not units[0][1]
+        if good:
+            secs = _sections(units[0][0])
+            good = _contiguous(secs, loop.loop_order == common.LoopOrder.BACKWARD)
+        ok.append(good)
+    runs, cur = [], []
+    for n, good in enumerate(ok):
+        if good:
+            cur.append(n)
+        else:
+            if len(cur) >= 2:
+                runs.append(cur)
+            cur = []
+    if len(cur) >= 2:
+        runs.append(cur)
+    out = []
+    for run in runs:
+        while len(run) >= 2:  # shrink from the end until the column-locality condition holds
+            written, offset = set(), set()
+            for n in run:
+                for _, h in units_by_loop[n][2][0][0]:
+                    for kind, acc, _, _ in _walk(h.body):
+                        name = str(acc.name)
+                        if kind == "w":
+                            written.add(name)
+                        off = acc.offset
+                        if isinstance(off, common.CartesianOffset) and (off.i or off.j):
+                            offset.add(name)
+            if written & offset:
+                run = run[:-1]
+            else:
+                break
+        if len(run) >= 2:
+            out.append(run)
+    return out
+
+
+def _field(fields, name):
+    return next(v for k, v in fields.items() if str(k) == name)
+
+
+class Analysis:
+    """Which fields of a run are cached in registers / pushed / popped / loaded / prefetched, per loop."""
+
+    def __init__(self, stencil: oir.Stencil, run_loops, fields, accessed_outside: Set[str]):
+        self.loops = run_loops            # [(loop, sections, backward)]
+        temps = {str(t.name) for t in stencil.declarations}
+        nl = len(run_loops)
+        acc: List[List[List[Tuple]]] = []  # accesses per loop / section
+        for loop, secs, _ in run_loops:
+            acc.append([[a for h in hs for a in _walk(h.body)] for _, hs in secs])
+        written_in = [set(str(a.name) for sec in la for k, a, _, _ in sec if k == "w") for la in acc]
+        touched_in = [set(str(a.name) for sec in la for _, a, _, _ in sec) for la in acc]
+        self.written = set().union(*written_in)
+        # ---- cached fields: float64 IJK fields written in the run, touched only at (0, 0, 0) and (0, 0, prev) ------
+        cached: Dict[str, Dict[str, Any]] = {}
+        for name in sorted(self.written):
+            f = _field(fields, name)
+            if not all(f["dims"]) or f["data_dims"] or f["dtype"] != common.DataType.FLOAT64:
+                continue
+            good = True
+            for n, (loop, secs, backward) in enumerate(run_loops):
+                prev = 1 if backward else -1
+                reads_prev = False
+                for s_idx, sec in enumerate(acc[n]):
+                    for kind, a, _, _ in sec:
+                        if str(a.name) != name:
+                            continue
+                        off = a.offset
+                        if not isinstance(off, common.CartesianOffset) or off.i or off.j or a.data_index:
+                            good = False
+                        elif kind == "w" and off.k != 0:
+                            good = False
+                        elif kind == "r" and off.k not in (0, prev):
+                            good = False
+                        elif kind == "r" and off.k == prev:
+                            reads_prev = True
+                            if s_idx == 0:
+                                good = False  # the loop's first level would read a level the loop never visits
+                if reads_prev and not all(any(str(a.name) == name for _, a, _, _ in sec) for sec in acc[n]):
+                    good = False
+            if good:
+                cached[name] = {"store": name not in temps or name in accessed_outside}
+        self.cached = cached
+
+        def first_is_write(sec, name):
+            for kind, a, cond, _ in sec:
+                if str(a.name) != name or int(a.offset.k) != 0:
+                    continue
+                return kind == "w" and not cond
+            return False
+
+        needs_initial = [{name: not all(first_is_write(sec, name) for sec in acc[n])
+                          for name in cached if name in touched_in[n]} for n in range(nl)]
+        self.pop = [{name for name, need in needs_initial[n].items()
+                     if need and any(name in written_in[m] for m in range(n))} for n in range(nl)]
+        self.load = [{name for name, need in needs_initial[n].items()
+                      if need and name not in self.pop[n] and (name not in temps or name in accessed_outside)}
+                     for n in range(nl)]
+        self.push = [{name for name in cached if name in written_in[n]
+                      and any(name in self.pop[m] for m in range(n + 1, nl))} for n in range(nl)]
+        self.pushed = sorted(set().union(*self.push)) if self.push else []
+        self.reads_prev = [{str(a.name) for sec in acc[n] for k, a, _, _ in sec
+                            if k == "r" and str(a.name) in cached and int(a.offset.k) != 0} for n in range(nl)]
+        self.touched_in = touched_in
+        # ---- prefetch ring keys per loop: (field, di, dj) -> {"dk": offsets, "uses": [(section index, hexec)]} ------
+        self.ring: List[Dict[Tuple[str, int, int], Dict[str, Any]]] = []
+        ring_dtypes = (common.DataType.FLOAT64, common.DataType.FLOAT32, common.DataType.INT64, common.DataType.INT32)
+        for n, (loop, secs, backward) in enumerate(run_loops):
+            keys: Dict[Tuple[str, int, int], Dict[str, Any]] = {}
+            for s_idx, (_, hs) in enumerate(secs):
+                for h in hs:
+                    for kind, a, _, restricted in _walk(h.body):
+                        name = str(a.name)
+                        if kind != "r" or name in cached or name in self.written:
+                            continue
+                        f = _field(fields, name)
+                        if (not isinstance(a.offset, common.CartesianOffset) or a.data_index or not all(f["dims"])
+                                or f["data_dims"] or f["dtype"] not in ring_dtypes):
+                            continue
+                        key = (name, int(a.offset.i), int(a.offset.j))
+                        e = keys.setdefault(key, {"dk": set(), "uses": [], "free": True})
+                        e["dk"].add(int(a.offset.k))
+                        if restricted:  # read inside horizontal(region[...]): its halo only exists inside the region
+                            e["free"] = False
+                        if not any(x == s_idx and y is h for x, y in e["uses"]):
+                            e["uses"].append((s_idx, h))
+            for name in self.load[n]:  # the level-start value of a cached field nobody in the run wrote before
+                e = keys.setdefault((name, 0, 0), {"dk": set(), "uses": [], "free": True})
+                e["dk"].add(0)
+                e["free"] = True
+                e["uses"] = [(s_idx, h) for s_idx, (_, hs) in enumerate(secs) for h in hs]
+            self.ring.append({k: v for k, v in keys.items() if v["free"] and v["uses"]})
+
+
+def pow2ceil(n: int) -> int:
+    p = 1
+    while p < n:
+        p *= 2
+    return p
+
+
+def emit(kname: str, stencil: oir.Stencil, run: List[int], units_by_loop, block_ext, fields, scalar_names,
+         accessed_outside: Set[str], L) -> Tuple[str, Dict[str, Any]]:
+    """CUDA source + launch metadata of the fused kernel for the vertical loops `run`.  `L` is the lowering module
+    (ExprGen, CTYPES, _interval_cond)."""
+    run_loops = []
+    for n in run:
+        _, loop, units = units_by_loop[n]
+        run_loops.append((loop, _sections(units[0][0]), loop.loop_order == common.LoopOrder.BACKWARD))
+    an = Analysis(stencil, run_loops, fields, accessed_outside)
+    all_h = [h for _, secs, _ in run_loops for _, hs in secs for h in hs]
+    exts = [block_ext[id(h)] for h in all_h]
+    ilo, ihi = min(e[0][0] for e in exts), max(e[0][1] for e in exts)
+    jlo, jhi = min(e[1][0] for e in exts), max(e[1][1] for e in exts)
+    locals_ = {d.name for h in all_h for d in h.declarations}
+    gen = L.ExprGen(fields, scalar_names, locals_, True)
+    never_written = {str(f) for f in fields} - an.written
+    read_anywhere = set().union(*an.touched_in)
+    gen.readonly = {n for n in never_written if n in read_anywhere}
+    gen.cf_cached = an.cached
+    NP = len(an.pushed)
+    pslot = {name: p for p, name in enumerate(an.pushed)}
+
+    # ---- ring layout: slots of 256 x 8 bytes; per loop the keys are laid out from slot 0 (loops reuse the region) ----
+    ring_slots = 0
+    ring_of_loop = []
+    for keys in an.ring:
+        off, table = 0, {}
+        for key in sorted(keys):
+            dks = keys[key]["dk"]
+            depth = pow2ceil(LEAD + (max(dks) - min(dks)) + 1)
+            table[key] = {"slot": off, "depth": depth, "dkmin": min(dks), "dkmax": max(dks), **keys[key]}
+            off += depth
+        ring_of_loop.append(table)
+        ring_slots = max(ring_slots, off)
+    span_max = max([t["dkmax"] - t["dkmin"] for table in ring_of_loop for t in table.values()], default=0)
+
+    def ct_of(name):
+        return L.CTYPES[_field(fields, name)["dtype"]]
+
+    size_of = {"double": 8, "float": 4, "int64_t": 8, "int32_t": 4}
+
+    def guard_text(h):
+        e = block_ext[id(h)]
+        return f"i >= {e[0][0]} && i < a.ni + ({e[0][1]}) && j >= {e[1][0]} && j < a.nj + ({e[1][1]})"
+
+    guards: Dict[int, str] = {}
+    by_text: Dict[str, str] = {}
+    G = []  # guard declarations (per tile)
+    for h in all_h:
+        text = guard_text(h)
+        if text not in by_text:
+            by_text[text] = f"g{len(by_text)}"
+            G.append(f"        const bool {by_text[text]} = live && {text};")
+        guards[id(h)] = by_text[text]
+
+    def index_at(name, di, dj, level):
+        f = _field(fields, name)
+        terms = []
+        if f["dims"][0]:
+            terms.append(f"(idx_t)(i + ({di})) * S0(a.{name}_s[0])")
+        if f["dims"][1]:
+            terms.append(f"(idx_t)(j + ({dj})) * (idx_t)a.{name}_s[1]")
+        if f["dims"][2]:
+            terms.append(f"(idx_t)({level}) * (idx_t)a.{name}_s[2]")
+        return " + ".join(terms) if terms else "0"
+
+    def fold(fn, items):
+        items = sorted(set(items))
+        text = items[0]
+        for x in items[1:]:
+            text = f"{fn}({text}, {x})"
+        return text
+
+    S = []  # kernel body
+    S.append("    typedef typename b200_idx<U>::type idx_t;")
+    for name in (str(f) for f in fields if str(f) in gen.readonly):
+        S.append(f"    const {ct_of(name)} *__restrict__ g_{name} = a.{name};")
+    S.append("    extern __shared__ __align__(16) unsigned char b200_smem[];")
+    S.append("    __shared__ unsigned cf_tmem_slot;")
+    S.append("    const int tid = (int)(threadIdx.y * blockDim.x + threadIdx.x);")
+    S.append("    double *const cf_ring = reinterpret_cast<double *>(b200_smem) + tid;")
+    S.append("    b200_stack cf_stk;")
+    S.append("    cf_stk.tmem = b200_stack_setup(&cf_tmem_slot);")
+    S.append(f"    cf_stk.smem = reinterpret_cast<double *>(b200_smem) + {ring_slots} * 256 + tid;")
+    S.append(f"    cf_stk.n_smem = a.cf_{kname}_smem;")
+    S.append("    cf_stk.nthreads = (long long)gridDim.x * 256;")
+    S.append(f"    cf_stk.spill = a.cf_{kname}_spill + (long long)blockIdx.x * 256 + tid;")
+    S.append(f"    const int cf_tiles_i = (a.ni + ({ihi - ilo}) + {BX - 1}) / {BX};")
+    S.append(f"    const int cf_tiles = cf_tiles_i * ((a.nj + ({jhi - jlo}) + {BY - 1}) / {BY});")
+    S.append("    for (int cf_tile = (int)blockIdx.x; cf_tile < cf_tiles; cf_tile += (int)gridDim.x) {")
+    S.append(f"        const int i = ({ilo}) + (cf_tile % cf_tiles_i) * {BX} + (int)threadIdx.x;")
+    S.append(f"        const int j = ({jlo}) + (cf_tile / cf_tiles_i) * {BY} + (int)threadIdx.y;")
+    S.append(f"        const bool live = i < a.ni + ({ihi}) && j < a.nj + ({jhi});")
+    S += G
+    for name in sorted(an.cached):
+        S.append(f"        double cur_{name} = 0.0, prev_{name} = 0.0;")
+
+    for n, (loop, secs, backward) in enumerate(run_loops):
+        step = -1 if backward else 1
+        table = ring_of_loop[n]
+        gen.cf_prev = 1 if backward else -1
+        gen.cf_ring = {}
+        S.append(f"        {{  // ---- vertical loop {run[n]}: {'BACKWARD' if backward else 'FORWARD'}")
+        issue = []  # the prefetch of one level, per ring key
+        order = sorted(table)
+        for q, key in enumerate(order):
+            t = table[key]
+            name, di, dj = key
+            ct = ct_of(name)
+            per = 8 // size_of[ct]
+            S.append(f"            {ct} *const rg{q} = reinterpret_cast<{ct} *>(cf_ring + {t['slot']} * 256);  // {name}[{di},{dj}]")
+            gen.cf_ring[key] = (f"rg{q}", t["depth"] - 1, 256 * per)
+            far = t["dkmax"] if step > 0 else t["dkmin"]
+            use_guards = sorted({guards[id(h)] for _, h in t["uses"]})
+            lows, highs = [], []
+            for s_idx, _ in t["uses"]:
+                lo, hi = L._interval_cond(secs[s_idx][0])
+                lows.append(f"({lo}) + ({t['dkmin']})")
+                highs.append(f"({hi}) + ({t['dkmax']})")
+            S.append(f"            const int lo{q} = {fold('min', lows)}, hi{q} = {fold('max', highs)};")
+            fn = "b200_cp_async8" if size_of[ct] == 8 else "b200_cp_async4"
+            issue.append(f"{{ const int lv = kv + ({step * LEAD + far}); const bool ok = ({' || '.join(use_guards)}) && "
+                         f"lv >= lo{q} && lv < hi{q}; {fn}(rg{q} + (lv & {t['depth'] - 1}) * {256 * per}, "
+                         f"a.{name} + (ok ? {index_at(name, di, dj, 'lv')} : 0), ok); }}")
+        lo0, hi0 = L._interval_cond(secs[0][0])
+        first = f"({hi0}) - 1" if backward else f"({lo0})"
+        if issue:
+            S.append("            auto cf_issue = [&](const int kv) {  // copy one more level of every input into the ring")
+            S += ["                " + x for x in issue]
+            S.append("                b200_cp_commit();")
+            S.append("            };")
+            S.append(f"            for (int t = {LEAD + span_max}; t >= 1; --t) cf_issue({first} - ({step}) * t);  // prologue")
+        pops, loads, pushes = sorted(an.pop[n]), sorted(an.load[n]), sorted(an.push[n])
+
+        def paired(todo, fmt2, fmt1):
+            out, todo = [], list(todo)
+            while todo:
+                a_name = todo.pop(0)
+                pa = pslot[a_name]
+                if todo and pslot[todo[0]] == pa + 1 and pa % 2 == 0 and NP % 2 == 0:
+                    out.append(fmt2.format(s=f"k * {NP} + {pa}", a=a_name, b=todo.pop(0)))
+                else:
+                    out.append(fmt1.format(s=f"k * {NP} + {pa}", a=a_name))
+            return out
+
+        for interval, hs in secs:
+            lo, hi = L._interval_cond(interval)
+            if backward:
+                S.append(f"            for (int k = ({hi}) - 1; k >= ({lo}); --k) {{")
+            else:
+                S.append(f"            for (int k = ({lo}); k < ({hi}); ++k) {{")
+            if issue:
+                S.append(f"                cf_issue(k); b200_cp_wait<{LEAD}>();")
+            if pops:
+                S.append("                __syncwarp();")
+                S += paired(pops, "                b200_stack_pop2(cf_stk, {s}, cur_{a}, cur_{b});",
+                            "                cur_{a} = b200_stack_pop(cf_stk, {s});")
+            for name in loads:
+                q = order.index((name, 0, 0))
+                S.append(f"                cur_{name} = rg{q}[(k & {table[(name, 0, 0)]['depth'] - 1}) * 256];")
+            for h in hs:
+                S.append(f"                if ({guards[id(h)]}) {{")
+                for d in sorted(h.declarations, key=lambda d: str(d.name)):
+                    S.append(" " * 20 + f"{L.CTYPES[d.dtype]} {d.name} = 0;")
+                S += gen.stmts(h.body, 20)
+                S.append("                }")
+            if pushes:
+                S.append("                __syncwarp();")
+                S += paired(pushes, "                b200_stack_push2(cf_stk, {s}, cur_{a}, cur_{b});",
+                            "                b200_stack_push(cf_stk, {s}, cur_{a});")
+            for name in sorted(an.reads_prev[n]):
+                S.append(f"                prev_{name} = cur_{name};")
+            S.append("            }")
+        if issue:
+            S.append("            b200_cp_wait<0>();")
+        if pushes:
+            S.append("            b200_stack_fence();")
+        S.append("        }")
+    S.append("    }")
+    S.append("    b200_stack_teardown(&cf_tmem_slot);")
+    gen.cf_ring, gen.cf_cached = {}, {}
+
+    src = [f"template <bool U> __device__ __forceinline__ void {kname}_impl(const Args &a)", "{"] + S + ["}"]
+    for suffix, flag in (("", "false"), ("_u", "true")):
+        src.append(f'extern "C" __global__ void __launch_bounds__({BX * BY}, 1) {kname}{suffix}(const Args a) '
+                   f"{{ {kname}_impl<{flag}>(a); }}")
+    meta = {"name": kname, "kind": "colfuse", "block": [BX, BY], "i_ext": [int(ilo), int(ihi)], "j_ext": [int(jlo), int(jhi)],
+            "ring_slots": int(ring_slots), "stack_values_per_level": NP, "loops": [int(x) for x in run],
+            "cached": sorted(an.cached), "pushed": list(an.pushed),
+            "private": sorted(nm for nm, c in an.cached.items() if not c["store"])}
+    return "\n".join(src), meta

@@ -40,7 +40,7 @@ SHIM = r"""
 #include <algorithm>
 using std::isnan; using std::isinf; using std::isfinite; using std::min; using std::max;
 struct emu_dim3 { unsigned x, y, z; };
-static thread_local emu_dim3 blockIdx, blockDim, threadIdx;
+static thread_local emu_dim3 blockIdx, blockDim, threadIdx, gridDim;
 #define __shared__ static
 #define __align__(x) alignas(x)
 #include <sys/mman.h>
@@ -60,7 +60,54 @@ static unsigned char *emu_map_window(size_t bytes, int mode, void **base, size_t
     *base = p;
     return p + page + (mode ? (body - bytes) / 16 * 16 : 0);
 }
-#define __syncthreads() emu_barrier->arrive_and_wait()
+#define __syncthreads() do { if (emu_barrier) emu_barrier->arrive_and_wait(); } while (0)
+#define __syncwarp()
+// host forms of the fused column kernels' helpers (lowering.PRELUDE): cp.async is an immediate copy, the value
+// stack's Tensor-Memory part a per-thread array.  Threads of these kernels never communicate, so the launcher runs
+// them one after the other, each to completion.
+#include <cstring>
+static inline void b200_cp_async8(void *dst, const void *src, bool valid) { if (valid) memcpy(dst, src, 8); else memset(dst, 0, 8); }
+static inline void b200_cp_async4(void *dst, const void *src, bool valid) { if (valid) memcpy(dst, src, 4); else memset(dst, 0, 4); }
+static inline void b200_cp_commit() {}
+template <int N> static inline void b200_cp_wait() {}
+#define B200_STK_TMEM 128
+static double emu_tmem[1024][B200_STK_TMEM];
+struct b200_stack { unsigned tmem; double *smem; double *spill; int n_smem; long long nthreads; };
+static inline unsigned b200_stack_setup(unsigned *slot) { return threadIdx.y * blockDim.x + threadIdx.x; }
+static inline void b200_stack_teardown(unsigned *) {}
+static inline void b200_stack_push(const b200_stack &st, int s, double v)
+{
+    if (s < B200_STK_TMEM) emu_tmem[st.tmem][s] = v;
+    else if (s - B200_STK_TMEM < st.n_smem) st.smem[(s - B200_STK_TMEM) * 256] = v;
+    else st.spill[(long long)(s - B200_STK_TMEM - st.n_smem) * st.nthreads] = v;
+}
+static inline double b200_stack_pop(const b200_stack &st, int s)
+{
+    if (s < B200_STK_TMEM) return emu_tmem[st.tmem][s];
+    if (s - B200_STK_TMEM < st.n_smem) return st.smem[(s - B200_STK_TMEM) * 256];
+    return st.spill[(long long)(s - B200_STK_TMEM - st.n_smem) * st.nthreads];
+}
+static inline void b200_stack_pop2(const b200_stack &st, int s, double &v0, double &v1) { v0 = b200_stack_pop(st, s); v1 = b200_stack_pop(st, s + 1); }
+static inline void b200_stack_push2(const b200_stack &st, int s, double v0, double v1) { b200_stack_push(st, s, v0); b200_stack_push(st, s + 1, v1); }
+static inline void b200_stack_fence() {}
+"""
+
+COLFUSE_LAUNCHER = r"""
+extern "C" void emu_{name}(const Args *a, unsigned gx, unsigned gy, unsigned gz, unsigned bx, unsigned by, unsigned bz)
+{{
+    static unsigned char *window = (unsigned char *)aligned_alloc(128, 256 * 1024);
+    emu_smem = window;
+    emu_barrier = nullptr;
+    blockDim = emu_dim3{{bx, by, bz}};
+    gridDim = emu_dim3{{gx, gy, gz}};
+    for (unsigned X = 0; X < gx; ++X) {{
+        blockIdx = emu_dim3{{X, 0, 0}};
+        for (unsigned y = 0; y < by; ++y) for (unsigned x = 0; x < bx; ++x) {{
+            threadIdx = emu_dim3{{x, y, 0}};
+            {name}(*a);
+        }}
+    }}
+}}
 """
 
 TILE_LAUNCHER = r"""
@@ -104,7 +151,7 @@ extern "C" void emu_{name}(const Args *a, unsigned gx, unsigned gy, unsigned gz,
 
 
 def emulable(plan) -> bool:
-    return all(k["kind"] in ("point", "column", "tile") for k in plan["kernels"])
+    return all(k["kind"] in ("point", "column", "tile", "colfuse") for k in plan["kernels"])
 
 
 def _host_source(src: str, plan) -> str:
@@ -121,7 +168,7 @@ def _host_source(src: str, plan) -> str:
                   "unsigned char *b200_smem = emu_smem;", body)
     out = SHIM + body
     for k in plan["kernels"]:  # the generic-stride entry point: host arrays keep numpy's strides
-        out += (TILE_LAUNCHER if k["kind"] == "tile" else LAUNCHER).format(name=k["name"])
+        out += {"tile": TILE_LAUNCHER, "colfuse": COLFUSE_LAUNCHER}.get(k["kind"], LAUNCHER).format(name=k["name"])
     return out
 
 
@@ -212,6 +259,17 @@ def run(plan_dir: str, fields: dict, params: dict, origins: dict, domain, window
             block, grid = (*k["block"], 1), ((ni + ti - 1) // ti, (nj + tj - 1) // tj, nk)
             if nk <= 0:
                 continue
+        elif k["kind"] == "colfuse":  # persistent: fewer CTAs than tiles, so that the tile loop is exercised
+            bx, by = k["block"]
+            ntiles = ((wi + bx - 1) // bx) * ((wj + by - 1) // by)
+            ctas = max(1, min(ntiles, 3))
+            need = max(0, nk * k["stack_values_per_level"] - 128)
+            n_smem = min((need + 1) // 2, (250 * 1024 - k["ring_slots"] * 2048) // 2048)  # some in smem, the rest spilled
+            spill = np.zeros(max(1, (need - n_smem) * ctas * bx * by), dtype=np.float64)
+            keep.append(spill)
+            setattr(a, f"cf_{k['name']}_smem", n_smem)
+            setattr(a, f"cf_{k['name']}_spill", spill.ctypes.data)
+            block, grid = (bx, by, 1), (ctas, 1, 1)
         else:
             block, grid = (32, 4, 1), ((wi + 31) // 32, (wj + 3) // 4, 1)
         fn = getattr(lib, "emu_" + k["name"])

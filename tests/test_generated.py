@@ -62,7 +62,7 @@ def test_plan_is_loadable_without_gt4py(name):
     cls = generated.stencil_class(plan, os.path.join(GEN, name))
     assert set(cls._gt_field_info_) | set(cls._gt_parameter_info_) == set(plan["info"]["arg_names"])
     kinds = {k["kind"] for k in plan["kernels"]}
-    assert kinds <= {"point", "column", "tile"}
+    assert kinds <= {"point", "column", "tile", "colfuse"}
     src = open(os.path.join(GEN, name, "kernel.cu")).read()
     for k in plan["kernels"]:
         assert f" {k['name']}(const Args a)" in src and f" {k['name']}_u(const Args a)" in src
@@ -359,6 +359,12 @@ _SIZED = ["fv3_chain", "horizontal_diffusion", "horizontal_diffusion__tile", "ve
 # ... and every other definition of the registry fixtures once, at a ragged size
 _CASES = [(n, d) for n in _SIZED for d in _SIZES] + [(n, (67, 9, 7)) for n in NAMES
                                                       if not n.startswith("suite_") and n not in _SIZED]
+# fused FORWARD / BACKWARD column kernels (lowering_colfuse.py) with columns deep enough that the value stack leaves
+# Tensor Memory (128 values per thread) for shared memory and the spill area, and with more tiles than CTAs
+_CASES += [("vertical_advection_dycore", (9, 5, 80)), ("vertical_advection_dycore", (131, 3, 150)),
+           ("vertical_advection_dycore", (300, 7, 66)), ("tridiagonal_solver", (7, 4, 100)),
+           ("tridiagonal_solver", (260, 3, 70)), ("column_physics", (5, 6, 200)),
+           ("vertical_advection_dycore__f32", (40, 3, 90))]
 
 
 @pytest.mark.parametrize("name,domain", _CASES)

@@ -34,7 +34,9 @@ CASES = {
     "exec_info_diffusion": ((301, 203, 41), ["tile"], "_t"),
     "fv3_chain": ((300, 200, 40), ["tile"], "_t"),
     "horizontal_diffusion__tile": ((322, 197, 40), ["tile"], "_t"),
-    "column_physics": ((300, 200, 64), ["column", "column"], "_u"),
+    "column_physics": ((300, 200, 64), ["colfuse"], "_u"),          # fused FORWARD + BACKWARD (lowering_colfuse.py)
+    "vertical_advection_dycore": ((300, 131, 80), ["colfuse"], "_u"),  # lowered kernels (library matching off)
+    "tridiagonal_solver": ((257, 66, 80), ["colfuse"], "_u"),
     "vertical_advection_dycore__kcache": ((257, 130, 65), None, "_u"),
     "horizontal_region_with_conditional": ((300, 211, 40), None, None),
     "runtime_if": ((310, 200, 40), None, None),
@@ -97,6 +99,18 @@ def test_generated_kernel_at_a_size_that_crosses_boundaries(name):
     if suffix is not None and not EMU:
         first = type(impl)._last_entry_points[0]
         assert first.endswith(suffix), type(impl)._last_entry_points
+
+
+@pytest.mark.parametrize("nk", [3, 64, 65, 111, 200])
+def test_fused_column_kernel_over_column_depths(nk):
+    """Generated vadv with other externals (BET_M = 0.4: not the library's kernel) through the fused FORWARD / BACKWARD
+    template: NK = 64 / 65 straddle the Tensor-Memory part of the value stack (128 values per thread, 2 per level),
+    111 and 200 reach into shared memory; 3 is the minimum the stencil accepts."""
+    mk, gtscript, gt_storage = _setup()
+    fn, _ = mk.definitions()["vertical_advection_dycore"][:2]
+    impl = _compare(gtscript, gt_storage, mk, f"vadv_bet04_nk{nk}", fn, {"BET_M": 0.4, "BET_P": 0.6}, {}, {},
+                    (270, 37, nk), seed=nk)
+    assert [k["kind"] for k in impl._plan_["kernels"]] == ["colfuse"] and "library" not in impl._plan_
 
 
 def test_data_dimension_stencil_at_size():

@@ -32,6 +32,7 @@ def main():
     rng = np.random.default_rng(0)
     for d in args.plans:
         st = generated.load_plan(d, use_library=not args.no_library)
+        type(st).configure(device_sync=False)  # time the kernels, not a host round trip per call
         plan = type(st)._plan_
         fields, nbytes = {}, 0
         for f in plan["fields"]:
