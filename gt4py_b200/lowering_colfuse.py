@@ -212,16 +212,18 @@ class Analysis:
                                 or f["data_dims"] or f["dtype"] not in ring_dtypes):
                             continue
                         key = (name, int(a.offset.i), int(a.offset.j))
-                        e = keys.setdefault(key, {"dk": set(), "uses": [], "free": True})
+                        e = keys.setdefault(key, {"dk": set(), "uses": [], "free": True, "dk_by_sec": {}})
                         e["dk"].add(int(a.offset.k))
+                        e["dk_by_sec"].setdefault(s_idx, set()).add(int(a.offset.k))
                         if restricted:  # read inside horizontal(region[...]): its halo only exists inside the region
                             e["free"] = False
                         if not any(x == s_idx and y is h for x, y in e["uses"]):
                             e["uses"].append((s_idx, h))
             for name in self.load[n]:  # the level-start value of a cached field nobody in the run wrote before
-                e = keys.setdefault((name, 0, 0), {"dk": set(), "uses": [], "free": True})
+                e = keys.setdefault((name, 0, 0), {"dk": set(), "uses": [], "free": True, "dk_by_sec": {}})
                 e["dk"].add(0)
-                e["free"] = True
+                for s_idx in range(len(secs)):
+                    e["dk_by_sec"].setdefault(s_idx, set()).add(0)
                 e["uses"] = [(s_idx, h) for s_idx, (_, hs) in enumerate(secs) for h in hs]
             self.ring.append({k: v for k, v in keys.items() if v["free"] and v["uses"]})
 
@@ -348,10 +350,12 @@ def emit(kname: str, stencil: oir.Stencil, run: List[int], units_by_loop, block_
             far = t["dkmax"] if step > 0 else t["dkmin"]
             use_guards = sorted({guards[id(h)] for _, h in t["uses"]})
             lows, highs = [], []
-            for s_idx, _ in t["uses"]:
+            # levels any statement reads: per section its own K offsets (a section that reads only k and k+1 must not
+            # make the prefetch touch k-1 below its first level); the hull of the pieces lies inside the field
+            for s_idx, dks in sorted(t["dk_by_sec"].items()):
                 lo, hi = L._interval_cond(secs[s_idx][0])
-                lows.append(f"({lo}) + ({t['dkmin']})")
-                highs.append(f"({hi}) + ({t['dkmax']})")
+                lows.append(f"({lo}) + ({min(dks)})")
+                highs.append(f"({hi}) + ({max(dks)})")
             S.append(f"            const int lo{q} = {fold('min', lows)}, hi{q} = {fold('max', highs)};")
             fn = "b200_cp_async8" if size_of[ct] == 8 else "b200_cp_async4"
             issue.append(f"{{ const int lv = kv + ({step * LEAD + far}); const bool ok = ({' || '.join(use_guards)}) && "

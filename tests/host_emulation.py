@@ -66,8 +66,21 @@ static unsigned char *emu_map_window(size_t bytes, int mode, void **base, size_t
 // stack's Tensor-Memory part a per-thread array.  Threads of these kernels never communicate, so the launcher runs
 // them one after the other, each to completion.
 #include <cstring>
-static inline void b200_cp_async8(void *dst, const void *src, bool valid) { if (valid) memcpy(dst, src, 8); else memset(dst, 0, 8); }
-static inline void b200_cp_async4(void *dst, const void *src, bool valid) { if (valid) memcpy(dst, src, 4); else memset(dst, 0, 4); }
+// every prefetch must read inside one of the arrays the launch was given (registered by host_emulation.run): a
+// prefetch that runs past a field's first or last level aborts here instead of silently reading a neighbour
+#include <cstdio>
+static std::vector<std::pair<const char *, const char *>> emu_ranges;
+extern "C" void emu_clear_ranges() { emu_ranges.clear(); }
+extern "C" void emu_add_range(const void *lo, size_t bytes) { emu_ranges.emplace_back((const char *)lo, (const char *)lo + bytes); }
+static inline void emu_check_src(const void *src, size_t n)
+{
+    if (emu_ranges.empty()) return;
+    for (auto &r : emu_ranges) if ((const char *)src >= r.first && (const char *)src + n <= r.second) return;
+    fprintf(stderr, "host emulation: cp.async source %p outside every field of the launch\n", src);
+    abort();
+}
+static inline void b200_cp_async8(void *dst, const void *src, bool valid) { if (valid) { emu_check_src(src, 8); memcpy(dst, src, 8); } else memset(dst, 0, 8); }
+static inline void b200_cp_async4(void *dst, const void *src, bool valid) { if (valid) { emu_check_src(src, 4); memcpy(dst, src, 4); } else memset(dst, 0, 4); }
 static inline void b200_cp_commit() {}
 template <int N> static inline void b200_cp_wait() {}
 #define B200_STK_TMEM 128
@@ -244,6 +257,14 @@ def run(plan_dir: str, fields: dict, params: dict, origins: dict, domain, window
         getattr(a, t["name"] + "_s")[:] = strides
     for s in plan["scalars"]:
         setattr(a, s["name"], params[s["name"]])
+    if any(k["kind"] == "colfuse" for k in plan["kernels"]):  # bounds of every array, for the prefetch check
+        lib.emu_clear_ranges()
+        lib.emu_add_range.argtypes = [ctypes.c_void_p, ctypes.c_size_t]
+        for arr in list(fields.values()) + keep:
+            if arr is not None:
+                base = arr.base if isinstance(arr.base, np.ndarray) else arr
+                lo = min(arr.ctypes.data, base.ctypes.data)
+                lib.emu_add_range(lo, max(base.nbytes, arr.nbytes))
     for k in plan["kernels"]:  # launch geometry of generated.GeneratedStencil._launch
         wi = ni + k["i_ext"][1] - k["i_ext"][0]
         wj = nj + k["j_ext"][1] - k["j_ext"][0]
