@@ -74,7 +74,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-configs", action="store_true", help="skip the `configs` block (N = 1)")
     ap.add_argument("--no-parity", action="store_true")
-    ap.add_argument("--halo-mode", default="push", choices=["push", "pull"],
+    ap.add_argument("--halo-mode", default="push", choices=["push", "push2", "pull"],
                     help="N>1: halo refresh by pushing faces into the neighbours' staging buffers "
                          "or by pulling boxes out of the neighbours' fields; both over NVLink peer memory")
     ap.add_argument("--no-overlap", action="store_true",
@@ -362,7 +362,8 @@ def halo_leg(halo, groups, stream, gb, barrier, allmax, reps=50):
     return {"bytes_received_per_gpu_per_step": int(nbytes), "us_per_step": round(us, 2), "achieved": round(gbs, 1),
             "unit": "GB/s", "peak": 900.0, "frac": round(gbs / 900.0, 4),
             "peak_source": "NVLink 5 nominal, per direction per GPU (B200_PROFILING.md; measured peer copy 770 GB/s)",
-            "note": "faces of 1.3-2.6 MB and 2.5 KB corners: launch/flag latency, not link bandwidth, bounds it",
+            "note": "faces of 1.3-2.6 MB and 2.5 KB corners, one launch per refresh (push + unpack fused): launch / flag "
+                    "latency, not link bandwidth, bounds it",
             "launches_counted": (5 + reps) * len(groups[0]) * halo.launches_per_refresh}
 
 
@@ -509,6 +510,7 @@ def run_b200(args):
         # the parity model swaps array roles: set 0's out_field takes the in-role, its utens_stage the wcon-role
         pgroups[("in", id(h0["out_field"]))] = halo.add_group([(h0["out_field"], (2, 2, 0), dom, h_in)])
         pgroups[("w", id(v0["utens_stage"]))] = halo.add_group([(v0["utens_stage"], (0, 0, 0), dom, h_w)])
+        halo.enable_multi_stream()  # the timed loop refreshes on the halo stream, the parity model on the compute stream
         halo.finalize()
 
     stream = gb.Stream()

@@ -44,7 +44,7 @@ class HaloBox(Structure):
         ("src_stride", c_int64 * 3),
         ("dst_stride", c_int64 * 3),
         ("extent", c_int32 * 3),
-        ("reserved", c_int32),
+        ("elem_bytes", c_int32),
     ]
 
 

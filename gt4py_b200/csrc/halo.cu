@@ -24,7 +24,7 @@ struct HaloBox {
     double *dst;        // local pointer of the box's first element
     int64_t ss[3], ds[3];  // element strides
     int32_t n[3];          // extents (i, j, k)
-    int32_t pad;
+    int32_t pad;           // element size in bytes (0 = 8)
 };
 static_assert(sizeof(HaloBox) == sizeof(b200_halo_box), "ABI struct mismatch");
 
@@ -57,14 +57,50 @@ __device__ __forceinline__ unsigned long long read_flag(const unsigned long long
 //   1  PULL : post ready(s), wait neighbours' ready(s), copy (src = peer memory), post done(s)
 //   2  PUSH : copy (dst = the neighbour's contiguous staging buffer), then post ready(s)
 //   3  UNPACK: wait neighbours' ready(s), copy (local staging -> halo cells)
-// PUSH + UNPACK is the fast path: boundary faces are only 2 elements wide along the contiguous axis, and
+//   4  PUSH + UNPACK in ONE launch: boxes [0, nsplit) are pushed (the last of their blocks to finish posts
+//      ready(s)), boxes [nsplit, nboxes) are unpacked by blocks that first wait for the neighbours' ready(s).
+//      The push blocks have the lower block indices and the whole grid is far smaller than what a GPU keeps
+//      resident, so the waiting blocks never keep a push block from running.
+// PUSH / UNPACK is the fast path: boundary faces are only 2 elements wide along the contiguous axis, and
 // 16-byte peer LOADS are bound by NVLink round-trip latency x outstanding requests, while the pushed stores
 // are posted writes, coalesced because the staging buffer is contiguous.
+// HaloBox.pad = element size in bytes (0 = 8): fields of every dtype (and, box by box, every data index) travel.
+template <typename T>
+__device__ __forceinline__ void copy_box_generic(const HaloBox &b)
+{
+    const T *src = reinterpret_cast<const T *>(b.src);
+    T *dst = reinterpret_cast<T *>(b.dst);
+    const int64_t total = (int64_t)b.n[0] * b.n[1] * b.n[2];
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    auto off = [&](int64_t idx, const int64_t (&st)[3]) {
+        const int i = (int)(idx % b.n[0]);
+        const int64_t r = idx / b.n[0];
+        return i * st[0] + (r % b.n[1]) * st[1] + (r / b.n[1]) * st[2];
+    };
+    for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += 2 * stride) {
+        const int64_t idx2 = idx + stride;
+        const T v0 = src[off(idx, b.ss)];
+        T v1 = T();
+        if (idx2 < total) v1 = src[off(idx2, b.ss)];
+        dst[off(idx, b.ds)] = v0;
+        if (idx2 < total) dst[off(idx2, b.ds)] = v1;
+    }
+}
+
 __global__ void __launch_bounds__(256)
 halo_refresh_kernel(const HaloBox *__restrict__ boxes, HaloSync sync, unsigned long long step,
-                    unsigned int *arrive, int use_flags)
+                    unsigned int *arrive, int use_flags, int nsplit)
 {
-    const int mode = use_flags;
+    int mode = use_flags;
+    unsigned int push_blocks = gridDim.x * gridDim.y;
+    if (mode == 4) {
+        push_blocks = gridDim.x * (unsigned)nsplit;
+        mode = (int)blockIdx.y < nsplit ? 2 : 3;
+        // nothing to push (e.g. the rank at the open end of a one-sided halo): the neighbours still wait for this
+        // rank's ready(s)
+        if (nsplit == 0 && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0)
+            for (int p = 0; p < sync.npeers; ++p) post_flag(sync.post_ready[p], step);
+    }
     if (mode == 1 || mode == 3) {
         if (threadIdx.x == 0) {
             if (mode == 1 && blockIdx.x == 0 && blockIdx.y == 0)
@@ -75,9 +111,9 @@ halo_refresh_kernel(const HaloBox *__restrict__ boxes, HaloSync sync, unsigned l
         __syncthreads();
     }
     const HaloBox b = boxes[blockIdx.y];
-    const int64_t total = (int64_t)b.n[0] * b.n[1] * b.n[2];
     const int64_t rows = (int64_t)b.n[1] * b.n[2];
-    if ((b.n[0] & 1) == 0 && b.ss[0] == 1 && b.ds[0] == 1 &&
+    const int elem = b.pad ? b.pad : 8;
+    if (elem == 8 && (b.n[0] & 1) == 0 && b.ss[0] == 1 && b.ds[0] == 1 &&
         ((reinterpret_cast<uintptr_t>(b.src) | reinterpret_cast<uintptr_t>(b.dst)) & 15) == 0 &&
         ((b.ss[1] | b.ss[2] | b.ds[1] | b.ds[2]) & 1) == 0) {
         // 128-bit path: pairs along the contiguous axis; two independent peer loads in flight per thread
@@ -102,28 +138,20 @@ halo_refresh_kernel(const HaloBox *__restrict__ boxes, HaloSync sync, unsigned l
             *reinterpret_cast<double2 *>(dst_of(idx)) = v0;
             if (idx2 < npairs) *reinterpret_cast<double2 *>(dst_of(idx2)) = v1;
         }
+    } else if (elem == 8) {
+        copy_box_generic<double>(b);
+    } else if (elem == 4) {
+        copy_box_generic<uint32_t>(b);
+    } else if (elem == 2) {
+        copy_box_generic<uint16_t>(b);
     } else {
-        const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-        auto off = [&](int64_t idx, const int64_t (&st)[3]) {
-            const int i = (int)(idx % b.n[0]);
-            const int64_t r = idx / b.n[0];
-            return i * st[0] + (r % b.n[1]) * st[1] + (r / b.n[1]) * st[2];
-        };
-        for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += 2 * stride) {
-            const int64_t idx2 = idx + stride;
-            const double v0 = b.src[off(idx, b.ss)];
-            double v1 = 0.0;
-            if (idx2 < total) v1 = b.src[off(idx2, b.ss)];
-            b.dst[off(idx, b.ds)] = v0;
-            if (idx2 < total) b.dst[off(idx2, b.ds)] = v1;
-        }
+        copy_box_generic<uint8_t>(b);
     }
     if (mode == 1 || mode == 2) {
         __syncthreads();
         if (threadIdx.x == 0) {
             __threadfence_system();  // this block's (peer) stores are visible before the flag
-            const unsigned int nblocks = gridDim.x * gridDim.y;
-            if (atomicAdd(arrive, 1u) == nblocks - 1) {
+            if (atomicAdd(arrive, 1u) == push_blocks - 1) {
                 *arrive = 0;  // ready for the next launch (stream order)
                 __threadfence_system();
                 for (int p = 0; p < sync.npeers; ++p)
@@ -174,8 +202,14 @@ int b200_halo_refresh(const b200_halo_box *boxes_dev, int nboxes, int blocks_per
                       void *stream)
 {
     using namespace b200;
+    // modes 0-3; mode 4 + 8 * nsplit: push boxes [0, nsplit) and unpack boxes [nsplit, nboxes) in one launch
+    const int nsplit = use_flags >= 4 ? (use_flags - 4) / 8 : 0;
+    if (use_flags >= 4) {
+        B200_REQUIRE((use_flags - 4) % 8 == 0 && nsplit <= nboxes, "halo_refresh: bad fused-mode encoding %d", use_flags);
+        use_flags = 4;
+    }
     B200_REQUIRE(nboxes >= 0 && blocks_per_box > 0, "halo_refresh: bad launch shape");
-    B200_REQUIRE(use_flags >= 0 && use_flags <= 3, "halo_refresh: unknown mode %d", use_flags);
+    B200_REQUIRE(use_flags >= 0 && use_flags <= 4, "halo_refresh: unknown mode %d", use_flags);
     if (nboxes == 0 && !use_flags) return B200_OK;
     B200_REQUIRE(nboxes == 0 || boxes_dev, "halo_refresh: boxes is null");
     HaloSync s;
@@ -197,7 +231,7 @@ int b200_halo_refresh(const b200_halo_box *boxes_dev, int nboxes, int blocks_per
         grid = dim3(1, 1);
     }
     halo_refresh_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<const HaloBox *>(boxes_dev), s,
-                                                                 (unsigned long long)step, arrive_dev, use_flags);
+                                                                 (unsigned long long)step, arrive_dev, use_flags, nsplit);
     B200_CUDA_CHECK(cudaGetLastError());
     return B200_OK;
 }

@@ -137,22 +137,30 @@ class HaloExchanger:
     """Refreshes the halos of registered device fields from the neighbour ranks.
 
     mode "push" (default): every rank packs its boundary faces straight into its neighbours' contiguous
-    staging buffers (coalesced posted writes over NVLink), posts a step-numbered flag, and each rank then
-    unpacks its own staging buffer into its halo cells -- two small kernels per refresh, staging double
-    buffered by step parity.  mode "pull": one kernel loads the boxes out of the neighbours' fields (simple,
-    but 16-byte peer loads are latency bound: 0.3 ms for the 1024 x 80 faces vs 20 us pushed).
+    staging buffers (coalesced posted writes over NVLink), posts a step-numbered flag, and then unpacks its own
+    staging buffer into its halo cells once its neighbours' flags have arrived -- ONE kernel launch per refresh
+    (b200_halo_refresh mode 4), staging double buffered by step parity.  mode "push2": the same as two launches
+    (push, then unpack).  mode "pull": one kernel loads the boxes out of the neighbours' fields (simple, but
+    16-byte peer loads are latency bound: 0.3 ms for the 1024 x 80 faces vs 20 us pushed).
+
+    Fields of any dtype with (I, J, K) leading axes and any number of data dimensions are supported (a box per
+    data index).  ORDERING: the staging buffers are reused every second refresh, which is safe because a rank's
+    refreshes execute in issue order: refreshes issued on different streams are chained with events by this class
+    (`enable_multi_stream()`; `refresh` then makes the stream wait for the previous refresh of this exchanger), and
+    every rank must issue the same sequence of refreshes.
     """
 
     ITEMS_PER_THREAD = 2
     MAX_BLOCKS_PER_BOX = 1024
+    RESIDENT_BLOCKS = 444  # 3 CTAs of 256 threads per SM: co-resident even beside a persistent compute kernel
 
     def __init__(self, comm, decomp: Decomposition, use_flags: bool = True, mode: str = "push"):
         """`use_flags=False` skips the inter-rank flag protocol: only for single-process emulations that
         run several ranks on ONE device and order them on the host (see `refresh_local`)."""
         from . import _lib, storage
 
-        if mode not in ("push", "pull"):
-            raise ValueError("mode must be 'push' or 'pull'")
+        if mode not in ("push", "push2", "pull"):
+            raise ValueError("mode must be 'push', 'push2' or 'pull'")
         self.mode = mode
         self.use_flags = bool(use_flags)
         self._lib, self._storage = _lib, storage
@@ -160,7 +168,9 @@ class HaloExchanger:
         self._groups: List[List[Tuple[object, tuple, tuple, tuple]]] = []
         self._finalized = False
         self.step = 0
-        self.launches_per_refresh = 2 if mode == "push" else 1
+        self.launches_per_refresh = 2 if mode == "push2" else 1
+        self._last_stream_key = None
+        self._last_event = None
 
     # -- registration ---------------------------------------------------------------------------------
     def add_group(self, fields: Sequence[Tuple[object, Sequence[int], Sequence[int], Sequence[Tuple[int, int]]]]) -> int:
@@ -170,21 +180,23 @@ class HaloExchanger:
             raise RuntimeError("HaloExchanger: add_group after finalize")
         group = []
         for arr, origin, domain, halo in fields:
-            if arr.dtype != np.float64 or arr.ndim != 3:
-                raise TypeError("halo refresh supports 3-D float64 fields")
+            if arr.ndim < 3 or arr.dtype.itemsize not in (1, 2, 4, 8):
+                raise TypeError("halo refresh needs fields with (I, J, K) leading axes and 1/2/4/8-byte elements")
             group.append((arr, tuple(int(o) for o in origin), tuple(int(d) for d in domain),
                           tuple((int(a), int(b)) for a, b in halo)))
         self._groups.append(group)
         return len(self._groups) - 1
 
     def _boxes_of(self, rank: int, group) -> List[Tuple[int, BoxSpec, int]]:
-        """(field index, box, staging offset in elements) of everything `rank` receives for `group`."""
+        """(field index, box, staging offset in BYTES, data index) of everything `rank` receives for `group`."""
         dec = Decomposition(self.decomp.world, rank, self.decomp.px_count, self.decomp.py_count)
         out, off = [], 0
-        for f, (_, origin, domain, halo) in enumerate(group):
-            for b in halo_boxes(dec, origin, domain, halo):
-                out.append((f, b, off))
-                off += b.extent[0] * b.extent[1] * b.extent[2]
+        for f, (arr, origin, domain, halo) in enumerate(group):
+            item = arr.dtype.itemsize
+            for b in halo_boxes(dec, origin[:3], domain, halo):
+                for data_index in np.ndindex(*arr.shape[3:]):
+                    out.append((f, b, off, tuple(int(x) for x in data_index)))
+                    off += (b.extent[0] * b.extent[1] * b.extent[2] * item + 15) // 16 * 16
         return out
 
     def finalize(self):
@@ -205,9 +217,14 @@ class HaloExchanger:
         self._flag_buf = self._storage._Buffer(16 * 8 + 8)
         L.check(lib.b200_memset(c_void_p(self._flag_buf.ptr), 0, self._flag_buf.nbytes, None))
         # staging: what this rank receives per refresh, two parities
-        self._stage_elems = max([sum(b.extent[0] * b.extent[1] * b.extent[2] for _, b, _ in self._boxes_of(self.decomp.rank, g))
-                                 for g in self._groups] or [0])
-        self._stage_half = (self._stage_elems * 8 + 255) // 256 * 256
+        def stage_bytes(g):
+            entries = self._boxes_of(self.decomp.rank, g)
+            if not entries:
+                return 0
+            f, b, off, _ = entries[-1]
+            return off + (b.extent[0] * b.extent[1] * b.extent[2] * g[f][0].dtype.itemsize + 15) // 16 * 16
+
+        self._stage_half = (max([stage_bytes(g) for g in self._groups] or [0]) + 255) // 256 * 256
         self._stage_buf = self._storage._Buffer(max(2 * self._stage_half, 256))
         L.synchronize()
 
@@ -245,7 +262,7 @@ class HaloExchanger:
         # synchronisation partners: every neighbour that exists in a direction used either way
         used = set()
         for group in self._groups:
-            for _, b, _ in self._boxes_of(me, group):
+            for _, b, _, _ in self._boxes_of(me, group):
                 used.add(b.direction)
         for d in list(used):
             used.add((-d[0], -d[1]))
@@ -266,14 +283,22 @@ class HaloExchanger:
         L.check(lib.b200_memset(c_void_p(self._arrive.ptr), 0, 8, None))
         peers = sorted({self.decomp.neighbour(*d) for d in partners})
 
-        def box(src, sstr, dst, dstr, extent):
+        def box(src, sstr, dst, dstr, extent, item=8):
             hb = L.HaloBox()
             hb.src, hb.dst = src, dst
             for d in range(3):
                 hb.src_stride[d], hb.dst_stride[d], hb.extent[d] = sstr[d], dstr[d], extent[d]
+            hb.elem_bytes = item
             return hb
 
-        def upload(entries):
+        def at(base, strides, start, data_index):
+            """Address of element (start, data_index) of an array at `base` with byte `strides`."""
+            return base + sum(s * st for s, st in zip(tuple(start) + tuple(data_index), strides))
+
+        def upload(entries, resident=False):
+            """`resident`: the launch mixes pushing blocks with blocks that spin on the neighbours' flags (fused
+            mode): keep the whole grid small enough to be co-resident on the GPU (148 SMs x several CTAs), so that a
+            waiting block can never keep a pushing block from being scheduled."""
             n = len(entries)
             table = (L.HaloBox * max(n, 1))(*entries)
             dev = self._storage._Buffer(max(n, 1) * ctypes.sizeof(L.HaloBox))
@@ -281,6 +306,8 @@ class HaloExchanger:
                 L.check(lib.b200_memcpy_h2d(c_void_p(dev.ptr), ctypes.addressof(table), n * ctypes.sizeof(L.HaloBox), None))
             most = max([e.extent[0] * e.extent[1] * e.extent[2] for e in entries] or [1])
             blocks = min(self.MAX_BLOCKS_PER_BOX, max(1, -(-most // (2 * 256 * self.ITEMS_PER_THREAD))))
+            if resident:
+                blocks = max(1, min(blocks, self.RESIDENT_BLOCKS // max(n, 1)))
             return dev, n, blocks
 
         def dense(extent):
@@ -294,22 +321,25 @@ class HaloExchanger:
         self._poison = []
         for group in self._groups:
             entries = []
-            for f, b, _ in self._boxes_of(me, group):
+            for f, b, _, di in self._boxes_of(me, group):
                 arr = group[f][0]
-                dst = arr.ptr + sum(s * st for s, st in zip(b.dst_start, arr.strides))
-                entries.append(box(self._nan.ptr, (0, 0, 0), dst, [st // arr.dtype.itemsize for st in arr.strides], b.extent))
+                item = arr.dtype.itemsize
+                if arr.dtype.kind != "f" or item != 8:
+                    continue  # NaN poisoning is a float64 check
+                entries.append(box(self._nan.ptr, (0, 0, 0), at(arr.ptr, arr.strides, b.dst_start, di),
+                                   [st // item for st in arr.strides[:3]], b.extent, item))
             self._poison.append(upload(entries))
         self._tables = []
         for g, group in enumerate(self._groups):
             if self.mode == "pull":
                 entries = []
-                for f, b, _ in self._boxes_of(me, group):
+                for f, b, _, di in self._boxes_of(me, group):
                     arr = group[f][0]
                     item = arr.dtype.itemsize
                     ref, offset, strides = everyone[b.src_rank]["fields"][g][f]
-                    src = mapped(b.src_rank, ref) + offset + sum(s * st for s, st in zip(b.src_start, strides))
-                    dst = arr.ptr + sum(s * st for s, st in zip(b.dst_start, arr.strides))
-                    entries.append(box(src, [st // item for st in strides], dst, [st // item for st in arr.strides], b.extent))
+                    src = at(mapped(b.src_rank, ref) + offset, strides, b.src_start, di)
+                    entries.append(box(src, [st // item for st in strides[:3]], at(arr.ptr, arr.strides, b.dst_start, di),
+                                       [st // item for st in arr.strides[:3]], b.extent, item))
                 self._tables.append({"pull": upload(entries)})
                 continue
             per_parity = []
@@ -317,20 +347,21 @@ class HaloExchanger:
                 push, unpack = [], []
                 for peer in peers:  # what each neighbour receives from me -> its staging buffer
                     stage = mapped(peer, everyone[peer]["staging"]) + parity * everyone[peer]["stage_half"]
-                    for f, b, off in self._boxes_of(peer, group):
+                    for f, b, off, di in self._boxes_of(peer, group):
                         if b.src_rank != me:
                             continue
                         arr = group[f][0]
                         item = arr.dtype.itemsize
-                        src = arr.ptr + sum(s * st for s, st in zip(b.src_start, arr.strides))
-                        push.append(box(src, [st // item for st in arr.strides], stage + off * 8, dense(b.extent), b.extent))
+                        push.append(box(at(arr.ptr, arr.strides, b.src_start, di), [st // item for st in arr.strides[:3]],
+                                        stage + off, dense(b.extent), b.extent, item))
                 mystage = self._stage_buf.ptr + parity * self._stage_half
-                for f, b, off in self._boxes_of(me, group):
+                for f, b, off, di in self._boxes_of(me, group):
                     arr = group[f][0]
                     item = arr.dtype.itemsize
-                    dst = arr.ptr + sum(s * st for s, st in zip(b.dst_start, arr.strides))
-                    unpack.append(box(mystage + off * 8, dense(b.extent), dst, [st // item for st in arr.strides], b.extent))
-                per_parity.append({"push": upload(push), "unpack": upload(unpack)})
+                    unpack.append(box(mystage + off, dense(b.extent), at(arr.ptr, arr.strides, b.dst_start, di),
+                                      [st // item for st in arr.strides[:3]], b.extent, item))
+                per_parity.append({"push": upload(push), "unpack": upload(unpack), "fused": upload(push + unpack, resident=True),
+                                   "nsplit": len(push)})
             self._tables.append(per_parity)
         L.synchronize()
         self._finalized = True
@@ -345,7 +376,7 @@ class HaloExchanger:
     def bytes_received(self, group: int) -> int:
         """Bytes this rank's halo cells of `group` receive from its neighbours per refresh."""
         total = 0
-        for f, b, _ in self._boxes_of(self.decomp.rank, self._groups[group]):
+        for f, b, _, _ in self._boxes_of(self.decomp.rank, self._groups[group]):
             total += int(b.extent[0]) * int(b.extent[1]) * int(b.extent[2]) * self._groups[group][f][0].dtype.itemsize
         return total
 
@@ -362,13 +393,36 @@ class HaloExchanger:
             raise RuntimeError("HaloExchanger: call finalize() first")
         if not self.use_flags:
             raise RuntimeError("HaloExchanger without flags: use HaloExchanger.refresh_local(exchangers, group)")
+        self._chain(stream)
         self.step += 1
         if self.mode == "pull":
             self._launch(self._tables[group]["pull"], 1, stream)
-        else:
+        elif self.mode == "push2":
             t = self._tables[group][self.step & 1]
             self._launch(t["push"], 2, stream)
             self._launch(t["unpack"], 3, stream)
+        else:
+            t = self._tables[group][self.step & 1]
+            self._launch(t["fused"], 4 + 8 * t["nsplit"], stream)
+        if self._last_event is not None:
+            self._last_event.record(stream)
+
+    def _chain(self, stream):
+        """Refreshes of one exchanger must execute in issue order (staging reuse, step-numbered flags): a refresh
+        issued on another stream than the previous one first waits for it."""
+        L = self._lib
+        key = int(L.stream_handle(stream).value or 0)
+        if self._last_stream_key is not None and key != self._last_stream_key:
+            if self._last_event is None:
+                raise RuntimeError("HaloExchanger: refreshes on several streams need enable_multi_stream() before the "
+                                   "first refresh (every rank alike)")
+            L.check(L.lib().b200_stream_wait_event(L.stream_handle(stream), self._last_event.handle))
+        self._last_stream_key = key
+
+    def enable_multi_stream(self):
+        """Allow refreshes on different streams (an event after every refresh chains them)."""
+        if self._last_event is None:
+            self._last_event = self._lib.Event()
 
     @staticmethod
     def refresh_local(exchangers: Sequence["HaloExchanger"], group: int, stream=None):

@@ -201,7 +201,7 @@ typedef struct b200_halo_box {
     int64_t src_stride[3];  /* element strides I, J, K */
     int64_t dst_stride[3];
     int32_t extent[3];
-    int32_t reserved;
+    int32_t elem_bytes;     /* element size: 1, 2, 4 or 8 (0 = 8); src / dst are then pointers to that type */
 } b200_halo_box;
 
 #define B200_HALO_MAX_PEERS 8
@@ -219,8 +219,8 @@ B200_API int b200_ipc_close_mem_handle(void *dptr);
 /* boxes_dev: device array of nboxes boxes; arrive_dev: zero-initialised device counter.  `use_flags` is the
  * protocol mode: 0 = plain box copy (single-process tests, or the caller orders the ranks itself);
  * 1 = PULL (post ready, wait ready, copy from peer memory, post done); 2 = PUSH (copy into the neighbours'
- * staging buffers, then post ready); 3 = UNPACK (wait ready, copy local staging -> halo).  The fast path is
- * one PUSH launch followed by one UNPACK launch per refresh. */
+ * staging buffers, then post ready); 3 = UNPACK (wait ready, copy local staging -> halo); 4 + 8 * nsplit = PUSH of
+ * boxes [0, nsplit) and UNPACK of boxes [nsplit, nboxes) in ONE launch -- the fast path: one launch per refresh. */
 B200_API int b200_halo_refresh(const b200_halo_box *boxes_dev, int nboxes, int blocks_per_box,
                       const b200_halo_sync *sync, uint64_t step, unsigned int *arrive_dev,
                       int use_flags, void *stream);

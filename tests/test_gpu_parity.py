@@ -273,6 +273,67 @@ def test_halo_refresh_single_device_emulation(world, mode):
         assert np.array_equal(f["utens_stage"].asnumpy()[:ni], Vref[x * ni: (x + 1) * ni, y * nj: (y + 1) * nj])
 
 
+@pytest.mark.parametrize("mode", ["push", "pull"])
+def test_halo_refresh_other_dtypes_and_data_dimensions(mode):
+    """float32 with a data dimension, int32 and int8 fields, asymmetric halo widths: every halo cell that has an
+    owner must arrive, cells outside the global domain stay untouched (single-device emulation, 2 x 2 ranks)."""
+    from gt4py_b200.halo import Decomposition, HaloExchanger, halo_boxes
+    from tests import halo_helpers as hh
+
+    world, dom, halo = 4, (12, 10, 5), ((1, 2), (2, 1))
+    ni, nj, nk = dom
+    decs = [Decomposition.create(world, r) for r in range(world)]
+    px, py = decs[0].px_count, decs[0].py_count
+    rng = np.random.default_rng(5)
+    lo_i, hi_i, lo_j, hi_j = halo[0][0], halo[0][1], halo[1][0], halo[1][1]
+    gshape = (px * ni + lo_i + hi_i, py * nj + lo_j + hi_j, nk)
+    G = {"f32": rng.uniform(-1, 1, gshape + (2,)).astype(np.float32),
+         "i32": rng.integers(-1000, 1000, gshape).astype(np.int32),
+         "i8": rng.integers(-100, 100, gshape).astype(np.int8)}
+    origin = (lo_i, lo_j, 0)
+    exs, dev, want = [], [], []
+    for d in decs:
+        x, y = d.coords
+        fields, expect = {}, {}
+        for name, g in G.items():
+            loc = g[x * ni: x * ni + ni + lo_i + hi_i, y * nj: y * nj + nj + lo_j + hi_j].copy()
+            expect[name] = loc.copy()
+            for b in halo_boxes(d, origin, dom, halo):  # stale values in every cell a neighbour owns
+                loc[hh.box_slices(b.dst_start, b.extent)] = 77
+            dims = ["I", "J", "K"] + (["0"] if loc.ndim == 4 else [])
+            fields[name] = storage.from_array(loc, aligned_index=origin + (0,) * (loc.ndim - 3), dimensions=dims)
+        ex = HaloExchanger(None, d, use_flags=False, mode=mode)
+        ex.add_group([(fields[n], origin, dom, halo) for n in G])
+        exs.append(ex)
+        dev.append(fields)
+        want.append(expect)
+    HaloExchanger.finalize_local(exs)
+    HaloExchanger.refresh_local(exs, 0)
+    gb.synchronize()
+    for f, w in zip(dev, want):
+        for name in G:
+            assert np.array_equal(f[name].asnumpy(), w[name]), name
+
+
+def test_two_gpu_run_checks_halo_parity():
+    """With two or more devices: bench.py on 2 ranks (small blocks, few steps) -- real peers, flags and staging --
+    must report halo_parity true (its model changes the exchanged values every step, oracle/model_parity.py)."""
+    import json
+    import subprocess
+    import sys
+
+    if gb.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+           "127.0.0.1", "--master-port", "29533", os.path.join(root, "bench.py"), "--gpus", "2", "--domain", "256",
+           "192", "40", "--steps", "6", "--warmup", "3", "--no-e2e"]
+    r = subprocess.run(cmd, capture_output=True, text=True, cwd=root, timeout=600)
+    assert r.returncode == 0, r.stderr[-3000:]
+    line = json.loads([ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1])
+    assert line["n_gpus"] == 2 and line["halo_parity"] is True and line["parity"]["ok"] is True
+
+
 @pytest.mark.parametrize("chunks", [1, 3, 8])
 def test_host_pipeline_matches_oracle(chunks):
     """Host-buffer call path (chunked H2D / kernel / D2H on three streams): same bits as the oracle."""
