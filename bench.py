@@ -77,6 +77,10 @@ def parse_args():
     ap.add_argument("--halo-mode", default="push", choices=["push", "push2", "pull"],
                     help="N>1: halo refresh by pushing faces into the neighbours' staging buffers "
                          "or by pulling boxes out of the neighbours' fields; both over NVLink peer memory")
+    ap.add_argument("--split", action="store_true",
+                    help="N>1: run both stencils through halo.DistributedStencil (refresh on its own stream, interior of "
+                         "the domain meanwhile, boundary strips after it) instead of hiding one stencil's refresh behind "
+                         "the other stencil")
     ap.add_argument("--no-overlap", action="store_true",
                     help="N>1: run the halo exchange on the compute stream instead of beside it")
     return ap.parse_args()
@@ -368,7 +372,7 @@ def halo_leg(halo, groups, stream, gb, barrier, allmax, reps=50):
 
 
 # ---- the multi-step parity model (see oracle/model_parity.py) -----------------------------------------------------
-def model_parity(gb, storage, hd, va, hset, vset, base, dom, goff, gdims, halo, pgroups, stream, steps=2):
+def model_parity(gb, storage, hd, va, hset, vset, base, dom, goff, gdims, halo, pgroups, stream, steps=2, dstencils=None):
     """Run `steps` steps of the evolving model on the device and compare this rank's block with the single-domain
     oracle on the check windows.  Returns (ok, report)."""
     from oracle import model_parity as mp
@@ -391,6 +395,10 @@ def model_parity(gb, storage, hd, va, hset, vset, base, dom, goff, gdims, halo, 
                 g_in, g_w = pgroups[("in", id(x_in))], pgroups[("w", id(w))]
                 halo.poison(g_in, stream)
                 halo.poison(g_w, stream)
+                if dstencils:  # --split: refresh + interior + boundary strips inside the distributed stencils
+                    dstencils[("in", id(x_in))](x_in, x_out, hset["coeff"])
+                    dstencils[("w", id(w))](u, vset["u_stage"], w, vset["u_pos"], vset["utens"], dtr_stage=gen_dtr())
+                    continue
                 halo.refresh(g_w, stream)
                 halo.refresh(g_in, stream)
             hd(x_in, x_out, hset["coeff"], origin=(2, 2, 0), domain=dom)
@@ -497,24 +505,33 @@ def run_b200(args):
     type(hd).configure(device_sync=False)
     type(va).configure(device_sync=False)
 
-    halo, groups, pgroups = None, [], {}
+    halo, groups, pgroups, dstencils = None, [], {}, {}
     if world > 1:
         halo = halo_mod.HaloExchanger(halo_mod.TorchComm(dist), decomp, mode=args.halo_mode)
         h_in = halo_mod.halo_from_field_info(hd, "in_field")   # ((2, 2), (2, 2)) from field_info.boundary
         h_w = halo_mod.halo_from_field_info(va, "wcon")        # ((0, 1), (0, 0))
+        def register(arr, role):
+            """A halo group for `arr` in the in_field / wcon role (with --split: inside a DistributedStencil)."""
+            if args.split:
+                ds = (halo_mod.DistributedStencil(hd, halo, {"in_field": arr}, origin=(2, 2, 0), domain=dom) if role == "in"
+                      else halo_mod.DistributedStencil(va, halo, {"wcon": arr}, origin=(0, 0, 0), domain=dom))
+                dstencils[(role, id(arr))] = ds
+                g = ds.group
+            else:
+                g = halo.add_group([(arr, (2, 2, 0), dom, h_in)] if role == "in" else [(arr, (0, 0, 0), dom, h_w)])
+            pgroups[(role, id(arr))] = g
+            return g
+
         for h, v in zip(hsets, vsets):
-            g_w = halo.add_group([(v["wcon"], (0, 0, 0), dom, h_w)])
-            g_in = halo.add_group([(h["in_field"], (2, 2, 0), dom, h_in)])
-            groups.append((g_w, g_in))
-            pgroups[("w", id(v["wcon"]))], pgroups[("in", id(h["in_field"]))] = g_w, g_in
+            groups.append((register(v["wcon"], "w"), register(h["in_field"], "in")))
         # the parity model swaps array roles: set 0's out_field takes the in-role, its utens_stage the wcon-role
-        pgroups[("in", id(h0["out_field"]))] = halo.add_group([(h0["out_field"], (2, 2, 0), dom, h_in)])
-        pgroups[("w", id(v0["utens_stage"]))] = halo.add_group([(v0["utens_stage"], (0, 0, 0), dom, h_w)])
+        register(h0["out_field"], "in")
+        register(v0["utens_stage"], "w")
         halo.enable_multi_stream()  # the timed loop refreshes on the halo stream, the parity model on the compute stream
         halo.finalize()
 
     stream = gb.Stream()
-    overlap = halo is not None and not args.no_overlap
+    overlap = halo is not None and not args.no_overlap and not args.split
     stream_h = gb.Stream() if overlap else None          # halo exchange runs beside the compute stream
     ev_step, ev_wcon, ev_in = (gb.Event(), gb.Event(), gb.Event()) if overlap else (None, None, None)
     names = {}
@@ -533,6 +550,16 @@ def run_b200(args):
         and in_field's (8 neighbours) is hidden behind vadv; ev = (before first, between, after second kernel)."""
         s = i % len(hsets)
         h, v = hsets[s], vsets[s]
+        if args.split and halo is not None and refresh:
+            if ev is not None:
+                ev[0].record(stream)
+            dstencils[("in", id(h["in_field"]))](h["in_field"], h["out_field"], h["coeff"])
+            if ev is not None:
+                ev[1].record(stream)
+            dstencils[("w", id(v["wcon"]))](v["utens_stage"], v["u_stage"], v["wcon"], v["u_pos"], v["utens"], dtr_stage=dtr)
+            if ev is not None:
+                ev[2].record(stream)
+            return
         if overlap and refresh:
             g_w, g_in = groups[s]
             ev_step.record(stream)
@@ -613,7 +640,8 @@ def run_b200(args):
     parity = None
     if not args.no_parity:
         t_p = time.perf_counter()
-        ok, report = model_parity(gb, storage, hd, va, hsets[0], vsets[0], base, dom, goff, gdims, halo, pgroups, stream)
+        ok, report = model_parity(gb, storage, hd, va, hsets[0], vsets[0], base, dom, goff, gdims, halo, pgroups, stream,
+                                  dstencils=dstencils)
         all_ok = allmin(1.0 if ok else 0.0) == 1.0
         parity = {"ok": all_ok, "rank0_windows": report, "steps": 2, "seconds": round(time.perf_counter() - t_p, 2),
                   "how": "2 model steps with changing exchanged fields, received halo cells poisoned with NaN before "
@@ -639,6 +667,17 @@ def run_b200(args):
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu, port = cpu_baseline_block(args.steps, 2, budget_ref=20.0, budget_port=8.0)
 
+    # launches per step: the two stencils (x their pieces with --split) + the refresh launches
+    launches_per_step = 2
+    if halo is not None:
+        refreshes = 2 * (1 if args.halo_mode != "push2" else 2)  # 'push' may take 2 launches for large faces: upper bound below
+        if args.halo_mode == "push":
+            refreshes = sum(1 if halo.bytes_received(g) <= halo.FUSED_MAX_BYTES else 2 for g in groups[0])
+        pieces = 0
+        if args.split:
+            for ds in (dstencils[("in", id(hsets[0]["in_field"]))], dstencils[("w", id(vsets[0]["wcon"]))]):
+                pieces += (1 + len(ds.strips)) if (ds.interior is not None and ds.strips) else 1
+        launches_per_step = (pieces if args.split else 2) + refreshes
     rc = 0
     if rank == 0:
         line = {
@@ -654,12 +693,13 @@ def run_b200(args):
                                           f"index), {setup_s:.1f} s",
                        "halo_mode": args.halo_mode if world > 1 else None,
                        "halo_overlap": ("exchange on its own stream: wcon's exposed, in_field's hidden behind vadv"
-                                        if overlap else None)},
+                                        if overlap else ("DistributedStencil: refresh beside the interior, boundary "
+                                                         "strips after it" if (args.split and halo is not None) else None))},
             "effective_GBs": round(value / 2 * (ALG_BYTES["hdiff"] + ALG_BYTES["vadv"]) / 1e9, 1),
             "roofline": kernels[dominant], "kernels": kernels,
             "parity": parity, "configs": configs,
             "e2e": e2e, "cpu_baseline": cpu, "cpu_port": port, "clocks": clocks,
-            "gpu_launches": 2 * args.steps + (2 * halo.launches_per_refresh * args.steps if halo else 0),
+            "gpu_launches": launches_per_step * args.steps,
         }
         if halo is not None:
             line["halo_parity"] = None if parity is None else parity["ok"]

@@ -152,6 +152,7 @@ class HaloExchanger:
 
     ITEMS_PER_THREAD = 2
     MAX_BLOCKS_PER_BOX = 1024
+    FUSED_MAX_BYTES = 512 * 1024  # mode 'push': one fused launch per refresh up to this many received bytes
     RESIDENT_BLOCKS = 444  # 3 CTAs of 256 threads per SM: co-resident even beside a persistent compute kernel
 
     def __init__(self, comm, decomp: Decomposition, use_flags: bool = True, mode: str = "push"):
@@ -401,6 +402,12 @@ class HaloExchanger:
             t = self._tables[group][self.step & 1]
             self._launch(t["push"], 2, stream)
             self._launch(t["unpack"], 3, stream)
+        elif self.bytes_received(group) > self.FUSED_MAX_BYTES:
+            # large faces: two launches with full-size grids beat the co-resident single launch (measured at
+            # 2048 x 2048 x 80 on 2 x B200: 52 vs 59 us for both refreshes of a step, profiles/r2_bench_n2_*.json)
+            t = self._tables[group][self.step & 1]
+            self._launch(t["push"], 2, stream)
+            self._launch(t["unpack"], 3, stream)
         else:
             t = self._tables[group][self.step & 1]
             self._launch(t["fused"], 4 + 8 * t["nsplit"], stream)
@@ -455,3 +462,101 @@ class HaloExchanger:
             ex.add_group([(v["wcon"], (0, 0, 0), dom, ((0, 1), (0, 0)))])       # field_info['wcon'].boundary
         ex.finalize()
         return ex
+
+
+# ---- interior / boundary split: the exchange hidden behind the part of the stencil that does not need it ------------
+def split_domain(domain: Sequence[int], halo: Sequence[Tuple[int, int]], has_neighbour) -> Tuple[
+        Optional[Tuple[Tuple[int, int, int], Tuple[int, int, int]]], List[Tuple[Tuple[int, int, int], Tuple[int, int, int]]]]:
+    """Cut a compute domain into the INTERIOR, whose points read no halo cell that a neighbour rank owns, and up to
+    four BOUNDARY strips (west / east over the full J range, south / north between them), as (offset, extent) pairs
+    relative to the compute origin.  `halo` = ((lo_i, hi_i), (lo_j, hi_j)) are the widths the stencil reads around a
+    point (field_info.boundary); `has_neighbour(dx, dy)` says whether a rank exists on that side (at an open boundary
+    the halo cells are the caller's own data, so nothing has to be waited for there).  The pieces are disjoint and
+    cover the domain; a side without neighbour contributes no strip."""
+    ni, nj, nk = (int(d) for d in domain)
+    (lo_i, hi_i), (lo_j, hi_j) = halo
+    w = lo_i if has_neighbour(-1, 0) else 0   # a point within lo_i of the west edge reads the west neighbour's cells
+    e = hi_i if has_neighbour(1, 0) else 0
+    s_ = lo_j if has_neighbour(0, -1) else 0
+    n = hi_j if has_neighbour(0, 1) else 0
+    if w + e >= ni or s_ + n >= nj:  # too thin for an interior: everything is boundary
+        return None, [((0, 0, 0), (ni, nj, nk))]
+    strips = []
+    if w:
+        strips.append(((0, 0, 0), (w, nj, nk)))
+    if e:
+        strips.append(((ni - e, 0, 0), (e, nj, nk)))
+    if s_:
+        strips.append(((w, 0, 0), (ni - w - e, s_, nk)))
+    if n:
+        strips.append(((w, nj - n, 0), (ni - w - e, n, nk)))
+    return ((w, s_, 0), (ni - w - e, nj - s_ - n, nk)), strips
+
+
+def call_on_pieces(stencil, bound: Dict[str, object], full_origin: Dict[str, Tuple[int, ...]], pieces) -> None:
+    """Run `stencil` on each (offset, extent) piece of its compute domain: origins shifted by the offset."""
+    for offset, extent in pieces:
+        origin = {k: tuple(o + d for o, d in zip(v[:3], offset)) + tuple(v[3:]) for k, v in full_origin.items()}
+        stencil(**bound, origin=origin, domain=tuple(extent))
+
+
+class DistributedStencil:
+    """A stencil whose halo'd input fields are refreshed from the neighbour ranks as part of the call:
+
+        ds = DistributedStencil(stencil, exchanger, {"in_field": in_field}, origin=(2, 2, 0), domain=dom)
+        ds(in_field, out_field, coeff)        # per step; every rank alike
+
+    The halo widths come from ``stencil.field_info[name].boundary`` (backend/module_generator.py:80-96 in the
+    reference), the boxes from the exchanger's decomposition.  One call = (1) the refresh of the registered fields on
+    the exchanger's own stream, (2) at the same time the stencil on the INTERIOR of the domain -- the points that read
+    no neighbour-owned halo cell -- on the caller's stream, (3) once the refresh has arrived, the stencil on the
+    boundary strips.  This is the "exchange overlapped with interior compute on separate streams" of the north star.
+    `split=False` runs refresh -> whole domain in order instead.  Fields must be registered BEFORE exchanger.finalize().
+    Build the stencil with ``device_sync=False`` (the pieces are ordered by streams and events, not by host waits).
+    Not for stencils with ``horizontal(region[...])`` blocks: regions are relative to the domain of each call, and
+    neither the reference nor this backend has a notion of a global domain.
+    """
+
+    def __init__(self, stencil, exchanger: "HaloExchanger", halo_fields: Dict[str, object], *, origin, domain,
+                 split: bool = True):
+        from . import _lib
+
+        self.stencil, self.ex, self.split = stencil, exchanger, bool(split)
+        self.domain = tuple(int(d) for d in domain)
+        self.origin = origin if isinstance(origin, dict) else {"_all_": tuple(int(o) for o in origin)}
+        group, lo_i = [], [0, 0, 0, 0]
+        for name, arr in halo_fields.items():
+            h = halo_from_field_info(stencil, name)
+            org = self.origin.get(name, self.origin.get("_all_"))
+            group.append((arr, tuple(org)[:3], self.domain, h))
+            lo_i = [max(lo_i[0], h[0][0]), max(lo_i[1], h[0][1]), max(lo_i[2], h[1][0]), max(lo_i[3], h[1][1])]
+        self.halo = ((lo_i[0], lo_i[1]), (lo_i[2], lo_i[3]))
+        self.group = exchanger.add_group(group)
+        exchanger.enable_multi_stream()
+        self.interior, self.strips = split_domain(self.domain, self.halo,
+                                                  lambda dx, dy: exchanger.decomp.neighbour(dx, dy) is not None)
+        self.stream_h = _lib.Stream()
+        self.ev_start, self.ev_done = _lib.Event(), _lib.Event()
+
+    def __call__(self, *args, **kwargs):
+        from .stencil_object import current_stream
+
+        st = self.stencil
+        names = type(st)._arg_names_
+        bound = dict(zip(names, args))
+        bound.update(kwargs)
+        if not hasattr(self, "_full_origin"):
+            all_org = self.origin.get("_all_")
+            self._full_origin = {n: tuple(self.origin.get(n, all_org)) + (0,) * len(fi.data_dims)
+                                 for n, fi in st.field_info.items() if fi is not None}
+        stream = current_stream()
+        self.ev_start.record(stream)
+        self.stream_h.wait_event(self.ev_start)          # not before the producers of the fields on the caller's stream
+        self.ex.refresh(self.group, self.stream_h)
+        self.ev_done.record(self.stream_h)
+        do_split = self.split and self.interior is not None and self.strips
+        if do_split:
+            call_on_pieces(st, bound, self._full_origin, [self.interior])
+        L = self.ex._lib
+        L.check(L.lib().b200_stream_wait_event(L.stream_handle(stream), self.ev_done.handle))
+        call_on_pieces(st, bound, self._full_origin, self.strips if do_split else [((0, 0, 0), self.domain)])

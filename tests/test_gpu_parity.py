@@ -315,7 +315,34 @@ def test_halo_refresh_other_dtypes_and_data_dimensions(mode):
             assert np.array_equal(f[name].asnumpy(), w[name]), name
 
 
-def test_two_gpu_run_checks_halo_parity():
+@pytest.mark.parametrize("dom", [(70, 45, 9), (128, 64, 80)])
+def test_interior_plus_boundary_strips_equal_the_whole_call(dom):
+    """DistributedStencil's split (halo.split_domain + call_on_pieces): hdiff and vadv run piece by piece -- the
+    interior and the four / one boundary strips of a rank with neighbours on every side -- give the same bits as one
+    call over the whole domain (and as the oracle)."""
+    from gt4py_b200.halo import call_on_pieces, halo_from_field_info, split_domain
+
+    hd, va = stencils.HorizontalDiffusion(), stencils.VerticalAdvectionDycore()
+    f = gen.hdiff_inputs(*dom, seed=31)
+    d = {k: _dev(v, (2, 2, 0)) for k, v in f.items()}
+    interior, strips = split_domain(dom, halo_from_field_info(hd, "in_field"), lambda dx, dy: True)
+    assert interior is not None and len(strips) == 4
+    call_on_pieces(hd, d, {k: (2, 2, 0) for k in d}, [interior] + strips)
+    ref = oracle.hdiff(f["in_field"], f["out_field"].copy(), f["coeff"], domain=dom)
+    assert np.array_equal(d["out_field"].asnumpy(), ref)
+
+    f = gen.vadv_inputs(*dom, seed=32)
+    dtr = f.pop("dtr_stage")
+    d = {k: _dev(v, (0, 0, 0)) for k, v in f.items()}
+    interior, strips = split_domain(dom, halo_from_field_info(va, "wcon"), lambda dx, dy: True)
+    assert interior == ((0, 0, 0), (dom[0] - 1, dom[1], dom[2])) and strips == [((dom[0] - 1, 0, 0), (1, dom[1], dom[2]))]
+    call_on_pieces(va, dict(d, dtr_stage=dtr), {k: (0, 0, 0) for k in d}, [interior] + strips)
+    ref = oracle.vadv(f["utens_stage"].copy(), f["u_stage"], f["wcon"], f["u_pos"], f["utens"], dtr_stage=dtr, domain=dom)
+    assert np.array_equal(d["utens_stage"].asnumpy(), ref)
+
+
+@pytest.mark.parametrize("extra", [[], ["--split"]], ids=["overlap", "split"])
+def test_two_gpu_run_checks_halo_parity(extra):
     """With two or more devices: bench.py on 2 ranks (small blocks, few steps) -- real peers, flags and staging --
     must report halo_parity true (its model changes the exchanged values every step, oracle/model_parity.py)."""
     import json
@@ -327,7 +354,7 @@ def test_two_gpu_run_checks_halo_parity():
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
            "127.0.0.1", "--master-port", "29533", os.path.join(root, "bench.py"), "--gpus", "2", "--domain", "256",
-           "192", "40", "--steps", "6", "--warmup", "3", "--no-e2e"]
+           "192", "40", "--steps", "6", "--warmup", "3", "--no-e2e", *extra]
     r = subprocess.run(cmd, capture_output=True, text=True, cwd=root, timeout=600)
     assert r.returncode == 0, r.stderr[-3000:]
     line = json.loads([ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1])

@@ -113,3 +113,29 @@ def test_decomposed_stencils_match_global_oracle_gloo(world):
     result = mgr.dict()
     mp.spawn(_worker, args=(world, _free_port(), (12, 10, 5), result), nprocs=world, join=True)
     assert dict(result) == {r: (True, True) for r in range(world)}
+
+
+def test_split_domain_pieces_are_disjoint_and_cover_the_domain():
+    """Interior + boundary strips (halo.split_domain, the overlap scheme of DistributedStencil) tile the domain, the
+    interior stays `halo` away from every side that has a neighbour, open sides contribute no strip."""
+    from gt4py_b200.halo import Decomposition, split_domain
+
+    for world, grid in ((1, None), (2, None), (4, None), (8, None), (6, (3, 2))):
+        for rank in range(world):
+            dec = Decomposition.create(world, rank, grid)
+            for halo in (((2, 2), (2, 2)), ((0, 1), (0, 0)), ((3, 0), (1, 2))):
+                for dom in ((20, 14, 3), (5, 4, 2), (3, 40, 1)):
+                    interior, strips = split_domain(dom, halo, lambda dx, dy: dec.neighbour(dx, dy) is not None)
+                    cover = np.zeros(dom[:2], int)
+                    for o, e in ([interior] if interior else []) + strips:
+                        assert all(x > 0 for x in e) and e[2] == dom[2]
+                        cover[o[0]:o[0] + e[0], o[1]:o[1] + e[1]] += 1
+                    assert (cover == 1).all(), (world, rank, halo, dom)
+                    if interior is not None:
+                        (oi, oj, _), (ei, ej, _) = interior
+                        assert oi == (halo[0][0] if dec.neighbour(-1, 0) is not None else 0)
+                        assert dom[0] - oi - ei == (halo[0][1] if dec.neighbour(1, 0) is not None else 0)
+                        assert oj == (halo[1][0] if dec.neighbour(0, -1) is not None else 0)
+                        assert dom[1] - oj - ej == (halo[1][1] if dec.neighbour(0, 1) is not None else 0)
+                    if world == 1:
+                        assert strips == [] and interior == ((0, 0, 0), dom)
