@@ -63,6 +63,20 @@ class HaloSync(Structure):
     ]
 
 
+class _ScalarValue(ctypes.Union):
+    _fields_ = [("f64", c_double), ("f32", c_float), ("i64", c_int64), ("i32", c_int32), ("i16", ctypes.c_int16),
+                ("i8", ctypes.c_int8), ("b", ctypes.c_uint8)]
+
+
+class Scalar(Structure):
+    """struct b200_scalar"""
+
+    _fields_ = [("value", _ScalarValue), ("dtype", c_int32), ("reserved", c_int32)]
+
+
+SCALAR_MEMBER = {1: "b", 2: "i8", 3: "i16", 4: "i32", 5: "i64", 6: "f32", 7: "f64"}
+
+
 class Field(Structure):
     """struct b200_field"""
 
@@ -129,6 +143,10 @@ _PROTOTYPES = {
     "b200_module_get_kernel": ([_VP, c_char_p, POINTER(_VP)], c_int),
     "b200_kernel_set_smem": ([_VP, c_int], c_int),
     "b200_launch": ([_VP, POINTER(c_uint32), POINTER(c_uint32), c_uint32, _VP, POINTER(_VP), c_int], c_int),
+    "b200_plan_create": ([c_char_p, c_size_t, _VP, c_size_t, c_int, POINTER(_VP)], c_int),
+    "b200_plan_launch": ([_VP, POINTER(c_int64), POINTER(Field), c_int, POINTER(Scalar), c_int, _VP, c_int], c_int),
+    "b200_plan_destroy": ([_VP], c_int),
+    "b200_plan_last_entries": ([_VP, c_char_p, c_size_t], c_int),
 }
 
 

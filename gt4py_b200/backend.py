@@ -194,6 +194,9 @@ class B200Backend(BaseBackend):
             out.mkdir(parents=True, exist_ok=True)
             (out / "kernel.cu").write_text(source, encoding="utf-8")
             (out / "plan.json").write_text(json.dumps(plan, indent=1), encoding="utf-8")
+            from . import generated as _generated  # what a host without Python hands to b200_plan_create
+
+            (out / "plan.desc").write_text(_generated.plan_descriptor(plan), encoding="utf-8")
             self.builder.with_backend_data({"b200:plan_md5": hashlib.md5(source.encode()).hexdigest()})
             from . import generated  # nvcc -cubin now, so that the first call does not pay for it
 

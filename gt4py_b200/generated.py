@@ -54,6 +54,51 @@ def compile_cubin(src_path: str) -> str:
     return out
 
 
+def plan_descriptor(plan: Dict[str, Any]) -> str:
+    """The plan as the line-based text `b200_plan_create` parses (include/gt4py_b200.h): what a host without Python
+    needs besides the cubin.  The backend writes it as `plan.desc` next to `plan.json`."""
+    code = {k.name: v for k, v in _lib.DTYPE_CODES.items()}
+    L = [f"b200plan 1 {plan['name'].replace(' ', '_')}"]
+    for f in plan["fields"]:
+        d = f["dims"]
+        L.append(f"field {f['name']} {code[f['dtype']]} {int(d[0])} {int(d[1])} {int(d[2])} {len(f['data_dims'])}")
+    for s in plan["scalars"]:
+        L.append(f"scalar {s['name']} {code[s['dtype']]}")
+    for t in plan["temporaries"]:
+        d, (pi, pj) = t["dims"], t["pad"]
+        L.append(f"temp {t['name']} {code[t['dtype']]} {int(d[0])} {int(d[1])} {int(d[2])} {len(t['data_dims'])} "
+                 + "".join(f"{int(x)} " for x in t["data_dims"]) + f"{pi[0]} {pi[1]} {pj[0]} {pj[1]}")
+    for k in plan["kernels"]:
+        head = f"kernel {k['name']} {k['kind']} {k['i_ext'][0]} {k['i_ext'][1]} {k['j_ext'][0]} {k['j_ext'][1]}"
+        if k["kind"] == "point":
+            L.append(f"{head} {int(k.get('rows_per_thread', 1))}")
+        elif k["kind"] == "tile":
+            tma = k.get("tma")
+            L.append(f"{head} {k['tile'][0]} {k['tile'][1]} {k['block'][0]} {k['block'][1]} {k['smem_bytes']} "
+                     f"{1 if tma else 0} {tma['smem_bytes'] if tma else 0}")
+        elif k["kind"] == "colfuse":
+            L.append(f"{head} {k['block'][0]} {k['block'][1]} {k['ring_slots']} {k['stack_values_per_level']}")
+        else:
+            L.append(head)
+    for name, kind, ref, extra in plan["args"]:
+        if kind == "field":
+            L.append(f"member field {name} {int(extra)}")
+        elif kind == "tmap":
+            L.append(f"member tmap {name} {ref} {extra['kernel']} {extra['box'][0]} {extra['box'][1]} {extra['box'][2]}")
+        elif kind == "origin":
+            L.append(f"member origin {name} {ref}")
+        elif kind in ("cf_spill", "cf_smem"):
+            L.append(f"member {kind} {name} {ref}")
+        else:
+            L.append(f"member scalar {name} {code[ref]}")
+    lib = plan.get("library")
+    if lib is not None:
+        roles = " ".join(f"{r}={a}" for r, a in lib["args"].items())
+        L.append(f"library {lib['kernel']} {int(lib.get('limiter', 0))} {int(lib.get('min_k', 1))} {len(lib['args'])} {roles}")
+    L.append("end")
+    return "\n".join(L) + "\n"
+
+
 class _Module:
     """A loaded cubin and its kernels."""
 
@@ -121,6 +166,57 @@ class GeneratedStencil(StencilObject):
     SCRATCH_SETS = 8
     TMAP_ENTRIES = 256
 
+    @classmethod
+    def _cplan(cls):
+        """The stencil as ONE C-ABI object (b200_plan_create, csrc/plan.inl): the C side packs the argument block,
+        picks entry points and grids and owns scratch, TMA descriptors and spill areas."""
+        if cls.__dict__.get("_cplan_handle") is None:
+            cubin = compile_cubin(os.path.join(cls._dir_, cls._plan_.get("source", "kernel.cu")))
+            with open(cubin, "rb") as fh:
+                image = fh.read()
+            desc = plan_descriptor(cls._plan_).encode()
+            handle = c_void_p()
+            buf = ctypes.create_string_buffer(image, len(image))
+            _lib.check(_lib.lib().b200_plan_create(desc, len(desc), buf, len(image), 1, byref(handle)))
+            cls._cplan_handle = handle
+            cls._cplan_image = buf
+            cls._cplan_arrays = {}
+            cls._code = {f["name"]: _lib.DTYPE_CODES[np.dtype(f["dtype"])] for f in cls._plan_["fields"]}
+            cls._entries_buf = ctypes.create_string_buffer(512)
+        return cls._cplan_handle
+
+    def _launch_cplan(self, domain, fields, params, stream):
+        cls = type(self)
+        handle = cls._cplan()
+        specs = cls._plan_["fields"]
+        key = tuple(id(fields.get(f["name"])) for f in specs)
+        arr = cls._cplan_arrays.get(key)
+        if arr is None:  # the b200_field structs are cached per argument by StencilObject.run: identity is stable
+            arr = (_lib.Field * max(len(specs), 1))()
+            for n, f in enumerate(specs):
+                src = fields.get(f["name"])
+                if src is None:
+                    arr[n].ptr = None
+                    arr[n].dtype = cls._code[f["name"]]
+                    arr[n].ndim = f["ndim"]
+                else:
+                    ctypes.memmove(ctypes.byref(arr[n]), ctypes.byref(src), ctypes.sizeof(_lib.Field))
+            if len(cls._cplan_arrays) > 64:
+                cls._cplan_arrays.clear()
+            cls._cplan_arrays[key] = (arr, [fields.get(f["name"]) for f in specs])  # keeps the ids alive
+        else:
+            arr = arr[0]
+        scal = cls._plan_["scalars"]
+        sarr = (_lib.Scalar * max(len(scal), 1))()
+        for n, s in enumerate(scal):
+            c = _lib.DTYPE_CODES[np.dtype(s["dtype"])]
+            sarr[n].dtype = c
+            setattr(sarr[n].value, _lib.SCALAR_MEMBER[c], params[s["name"]])
+        _lib.check(_lib.lib().b200_plan_launch(handle, (ctypes.c_int64 * 3)(*domain), arr, len(specs), sarr, len(scal),
+                                               _lib.stream_handle(stream), 0))
+        _lib.lib().b200_plan_last_entries(handle, cls._entries_buf, 512)
+        cls._last_entry_points = [e for e in cls._entries_buf.value.decode().split(",") if e]
+
     def _temporaries(self, domain, stream=None):
         """Global scratch for the OIR temporaries, owned by the stencil class and cached per (domain, stream): two
         streams (or a captured graph and a live stream) running the same stencil never share temporaries, and a
@@ -185,6 +281,9 @@ class GeneratedStencil(StencilObject):
         lib_plan = cls._plan_.get("library")
         if lib_plan is not None and cls._use_library_ and domain[2] >= lib_plan.get("min_k", 1):
             return self._launch_library(lib_plan, domain, fields, params, stream)
+        if not _PY_LAUNCH:
+            return self._launch_cplan(domain, fields, params, stream)
+        # the same launch interpreted in Python (B200_PY_LAUNCH=1: kept for A/B runs of the call overhead)
         mod = cls._module()
         a = cls._Args()
         a.ni, a.nj, a.nk = domain
@@ -301,6 +400,7 @@ class GeneratedStencil(StencilObject):
                                               (ctypes.c_uint32 * 3)(*block), smem, sh, argp, 1))
 
 
+_PY_LAUNCH = os.environ.get("B200_PY_LAUNCH", "0") == "1"
 _COLFUSE_SMEM = 226 * 1024  # dynamic shared memory a fused column kernel may use (227 KB minus its static part)
 _SM_COUNT = []
 

@@ -191,6 +191,42 @@ B200_API int b200_tmap_encode(const b200_field *field, const uint32_t box[3], vo
 B200_API int b200_launch(void *kernel, const uint32_t grid[3], const uint32_t block[3],
                 uint32_t dynamic_smem_bytes, void *stream, void **args, int nargs);
 
+/* ---- a generated stencil as one object: the plan-level entry points (csrc/plan.inl) ------------------------------
+ * Replace the reference's per-stencil pybind11 entry `run_computation(domain, field, origin, ..., exec_info)`
+ * (/root/reference/src/gt4py/cartesian/backend/gtc_common.py:79-101, call site :157-163) for hosts in any language.
+ * `desc` is the text the backend writes next to the generated module at build time (`plan.desc`; format: one record
+ * per line -- `b200plan 1 <name>`, `field`, `scalar`, `temp`, `kernel`, `member`, optional `library`, `end` -- see
+ * gt4py_b200/generated.py:plan_descriptor), `image` the cubin of `kernel.cu` (nvcc -cubin -arch sm_100a -fmad=false).
+ * flags bit 0: never dispatch to the hand-written library kernel even if the plan names one.
+ * b200_plan_launch: `fields` in the order of the descriptor's `field` records (API order; ptr == NULL for a field the
+ * stencil does not reference), `scalars` in the order of its `scalar` records.  The plan packs the argument block,
+ * picks the entry point of every kernel (any strides / unit stride + 32-bit indices / TMA-staged), owns the global
+ * scratch of the OIR temporaries (per domain and stream), the TMA descriptors and the spill areas of the fused column
+ * kernels; all of it is freed by b200_plan_destroy.  Field memory stays the caller's.  sync != 0: return after the
+ * stream (or, for a NULL stream, the device) has been synchronised -- the reference's
+ * `cupy.cuda.Device(0).synchronize()` (gtc_common.py:288-296).  One launch at a time per plan (calls are serialised
+ * by a lock inside the plan). */
+typedef struct b200_scalar {
+    union {
+        double f64;
+        float f32;
+        int64_t i64;
+        int32_t i32;
+        int16_t i16;
+        int8_t i8;
+        uint8_t b;
+    } value;
+    int32_t dtype; /* B200_* code; must equal the descriptor's */
+    int32_t reserved;
+} b200_scalar;
+B200_API int b200_plan_create(const char *desc, size_t desc_bytes, const void *image, size_t image_bytes, int flags,
+                     void **plan);
+B200_API int b200_plan_launch(void *plan, const int64_t domain[3], const b200_field *fields, int nfields,
+                     const b200_scalar *scalars, int nscalars, void *stream, int sync);
+B200_API int b200_plan_destroy(void *plan);
+/* comma-separated entry points the last b200_plan_launch of this plan launched (e.g. "k0_0_t"; "library:<kernel>") */
+B200_API int b200_plan_last_entries(void *plan, char *buf, size_t n);
+
 /* ---- multi-GPU halo refresh over NVLink peer memory (csrc/halo.cu) ------------------------------
  * New functionality: the reference has no distributed layer.  One process per GPU;
  * a rank maps its neighbours' field allocations with CUDA IPC and pulls the halo boxes with one kernel.

@@ -177,3 +177,8 @@ int b200_ipc_close_mem_handle(void *) { UNSUP("b200_ipc_close_mem_handle"); }
 int b200_halo_refresh(const b200_halo_box *, int, int, const b200_halo_sync *, uint64_t, unsigned int *, int, void *) { UNSUP("b200_halo_refresh"); }
 int b200_halo_wait_done(const b200_halo_sync *, uint64_t, void *) { UNSUP("b200_halo_wait_done"); }
 }
+
+// the plan-level entry points: the product's own text (csrc/plan.inl) on top of the doubles above
+#define B200_PLAN_SET_ERROR(msg) set_error("%s", msg)
+#define B200_PLAN_COLFUSE_SMEM (226 * 1024)
+#include "../gt4py_b200/csrc/plan.inl"

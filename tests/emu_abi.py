@@ -22,7 +22,8 @@ ROOT = os.path.dirname(HERE)
 
 def build() -> str:
     src = os.path.join(HERE, "emu_abi.cpp")
-    deps = [src, os.path.join(ROOT, "include", "gt4py_b200.h"), os.path.join(ROOT, "gt4py_b200", "csrc", "synthetic.cuh")]
+    deps = [src, os.path.join(ROOT, "include", "gt4py_b200.h"), os.path.join(ROOT, "gt4py_b200", "csrc", "synthetic.cuh"),
+            os.path.join(ROOT, "gt4py_b200", "csrc", "plan.inl")]
     tag = hashlib.sha256(b"".join(open(d, "rb").read() for d in deps)).hexdigest()[:16]
     cache = os.path.join(tempfile.gettempdir(), "gt4py_b200_host_emulation")
     os.makedirs(cache, exist_ok=True)

@@ -50,6 +50,30 @@ def main():
         frozen = hd.freeze(origin={k: (2, 2, 0) for k in h}, domain=dom)
         fr = lambda: frozen(in_field=h["in_field"], out_field=h["out_field"], coeff=h["coeff"])  # noqa: E731
         out["frozen_us"] = timed(fr, args.calls)
+    # a generated stencil (the config-4 chain): argument packing / entry choice / grids in C (b200_plan_launch), or,
+    # with B200_PY_LAUNCH=1 in the environment, interpreted in Python as in round 1
+    from gt4py_b200 import generated
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    st = generated.load_plan(os.path.join(root, "tests", "golden", "generated", "fv3_chain"))
+    type(st).configure(device_sync=False)
+    cdom, hh = (64, 64, 8), 3
+    rng = np.random.default_rng(0)
+    cf = {k: storage.from_array(rng.uniform(-1, 1.5, (cdom[0] + 2 * hh, cdom[1] + 2 * hh, cdom[2])), aligned_index=(hh, hh, 0))
+          for k in ("phi", "u", "v")}
+    cf["out"] = storage.zeros(cdom)
+    org = {"_all_": (hh, hh, 0), "out": (0, 0, 0)}
+    out["generated"] = {"stencil": "fv3_chain (generated tile kernel)", "domain": list(cdom),
+                        "launch_path": "python" if os.environ.get("B200_PY_LAUNCH") == "1" else "b200_plan_launch"}
+    with gb.use_stream(stream):
+        full = lambda: st(cf["phi"], cf["u"], cf["v"], cf["out"], dt=0.05, alpha=0.03, origin=org, domain=cdom)  # noqa: E731
+        out["generated"]["call_us"] = timed(full, args.calls)
+        fast = lambda: st(cf["phi"], cf["u"], cf["v"], cf["out"], dt=0.05, alpha=0.03, origin=org, domain=cdom,  # noqa: E731
+                          validate_args=False)
+        out["generated"]["call_novalidate_us"] = timed(fast, args.calls)
+        fz = st.freeze(origin={"phi": (hh, hh, 0), "u": (hh, hh, 0), "v": (hh, hh, 0), "out": (0, 0, 0)}, domain=cdom)
+        fr2 = lambda: fz(phi=cf["phi"], u=cf["u"], v=cf["v"], out=cf["out"], dt=0.05, alpha=0.03)  # noqa: E731
+        out["generated"]["frozen_us"] = timed(fr2, args.calls)
     g = gb.Graph(stream)
     per_graph = 20
     with g:
