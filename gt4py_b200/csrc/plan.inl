@@ -102,7 +102,7 @@ struct Plan {
     std::vector<TempSpec> temps;
     std::vector<Member> members;
     std::vector<Kernel> kernels;
-    bool has_library = false, use_library = true;
+    bool has_library = false, use_library = true, no_tma = false;
     Library lib;
     size_t args_bytes = 0, off_ni = 0;
     std::vector<unsigned char> args;
@@ -299,6 +299,7 @@ static int create(const char *desc, size_t desc_bytes, const void *image, size_t
     if (!desc || !image || !out) return fail(B200_EINVAL, "plan_create: null argument");
     Plan *p = new Plan();
     p->use_library = (flags & 1) == 0;
+    p->no_tma = (flags & 2) != 0;
     int rc = parse(*p, std::string(desc, desc_bytes));
     if (!rc) rc = b200_module_load(image, image_bytes, &p->module);
     for (size_t n = 0; !rc && n < p->kernels.size(); ++n) {
@@ -451,7 +452,7 @@ static int launch(Plan &p, const int64_t dom[3], const b200_field *fields, int n
     put<int32_t>(p, p.off_ni + 8, (int32_t)nk);
     // ---- TMA descriptors of the staged inputs (cached per field layout; an incompatible layout -> plain entry) --------
     std::vector<int> tma_ok(p.kernels.size(), -1);  // -1 no staged input, 0 not usable, 1 usable
-    if (unit) {
+    if (unit && !p.no_tma) {
         std::map<int, int> shifts;
         for (size_t mi = 0; mi < p.members.size(); ++mi) {
             Member &m = p.members[mi];

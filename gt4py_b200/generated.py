@@ -177,7 +177,8 @@ class GeneratedStencil(StencilObject):
             desc = plan_descriptor(cls._plan_).encode()
             handle = c_void_p()
             buf = ctypes.create_string_buffer(image, len(image))
-            _lib.check(_lib.lib().b200_plan_create(desc, len(desc), buf, len(image), 1, byref(handle)))
+            flags = 1 | (2 if os.environ.get("B200_GENERATED_TMA", "1") == "0" else 0)
+            _lib.check(_lib.lib().b200_plan_create(desc, len(desc), buf, len(image), flags, byref(handle)))
             cls._cplan_handle = handle
             cls._cplan_image = buf
             cls._cplan_arrays = {}

@@ -197,7 +197,8 @@ B200_API int b200_launch(void *kernel, const uint32_t grid[3], const uint32_t bl
  * `desc` is the text the backend writes next to the generated module at build time (`plan.desc`; format: one record
  * per line -- `b200plan 1 <name>`, `field`, `scalar`, `temp`, `kernel`, `member`, optional `library`, `end` -- see
  * gt4py_b200/generated.py:plan_descriptor), `image` the cubin of `kernel.cu` (nvcc -cubin -arch sm_100a -fmad=false).
- * flags bit 0: never dispatch to the hand-written library kernel even if the plan names one.
+ * flags bit 0: never dispatch to the hand-written library kernel even if the plan names one; bit 1: never use the
+ * TMA-staged entry points (A/B runs).
  * b200_plan_launch: `fields` in the order of the descriptor's `field` records (API order; ptr == NULL for a field the
  * stencil does not reference), `scalars` in the order of its `scalar` records.  The plan packs the argument block,
  * picks the entry point of every kernel (any strides / unit stride + 32-bit indices / TMA-staged), owns the global
