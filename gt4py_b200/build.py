@@ -42,7 +42,7 @@ def needs_build() -> bool:
     if not os.path.exists(LIB):
         return True
     t = os.path.getmtime(LIB)
-    deps = sources() + glob.glob(os.path.join(CSRC, "*.cuh")) + [
+    deps = sources() + glob.glob(os.path.join(CSRC, "*.cuh")) + glob.glob(os.path.join(CSRC, "*.inl")) + [
         os.path.join(os.path.dirname(PKG), "include", "gt4py_b200.h")]
     return any(os.path.getmtime(d) > t for d in deps)
 

@@ -71,7 +71,7 @@ struct Kernel {
     std::string name;
     KernelKind kind;
     int ilo = 0, ihi = 0, jlo = 0, jhi = 0;
-    int rows = 1, ti = 0, tj = 0, bx = 0, by = 0, smem = 0, has_tma = 0, smem_tma = 0, ring_slots = 0, stack_values = 0;
+    int rows = 1, ti = 0, tj = 0, bx = 0, by = 0, smem = 0, has_tma = 0, smem_tma = 0, ring_slots = 0, stack_values = 0, stack_tmem = 128;
     void *entry = nullptr, *entry_u = nullptr, *entry_t = nullptr;
     void *spill = nullptr;
     size_t spill_bytes = 0;
@@ -204,7 +204,7 @@ static int parse(Plan &p, const std::string &text)
             if (kind == "point") { k.kind = K_POINT; ls >> k.rows; }
             else if (kind == "column") { k.kind = K_COLUMN; }
             else if (kind == "tile") { k.kind = K_TILE; ls >> k.ti >> k.tj >> k.bx >> k.by >> k.smem >> k.has_tma >> k.smem_tma; }
-            else if (kind == "colfuse") { k.kind = K_COLFUSE; ls >> k.bx >> k.by >> k.ring_slots >> k.stack_values; }
+            else if (kind == "colfuse") { k.kind = K_COLFUSE; ls >> k.bx >> k.by >> k.ring_slots >> k.stack_values >> k.stack_tmem; }
             else return fail(B200_EINVAL, "plan descriptor: unknown kernel kind '%s'", kind.c_str());
             if (!ls) return fail(B200_EINVAL, "plan descriptor: bad kernel line '%s'", line.c_str());
             p.kernels.push_back(k);
@@ -519,17 +519,18 @@ static int launch(Plan &p, const int64_t dom[3], const b200_field *fields, int n
             smem = (uint32_t)k.smem;
             if (tma_ok[n] == 1 && k.entry_t) { entry = k.entry_t; sfx = "_t"; smem = (uint32_t)k.smem_tma; }
         } else if (k.kind == K_COLFUSE) {
-            // persistent fused FORWARD / BACKWARD kernel: a CTA per SM walks 256-column tiles; the value stack beyond
-            // Tensor Memory (128 values per thread) goes to shared memory, then to an L2-resident spill area
+            // persistent fused FORWARD / BACKWARD kernel: a CTA per SM walks column tiles; the value stack beyond the
+            // thread's share of Tensor Memory goes to shared memory, then to an L2-resident spill area
             const int64_t ntiles = ((wi + k.bx - 1) / k.bx) * ((wj + k.by - 1) / k.by);
             const int64_t ctas = ntiles < p.sm_count ? (ntiles > 0 ? ntiles : 1) : p.sm_count;
-            int64_t need = nk * k.stack_values - 128;
+            const int64_t slot = (int64_t)k.bx * k.by * 8;  // one value (or one ring level) of every thread of the CTA
+            int64_t need = nk * k.stack_values - k.stack_tmem;
             if (need < 0) need = 0;
-            const int64_t ring = (int64_t)k.ring_slots * 2048;
-            int64_t n_smem = (B200_PLAN_COLFUSE_SMEM - ring) / 2048;
+            const int64_t ring = (int64_t)k.ring_slots * slot;
+            int64_t n_smem = (B200_PLAN_COLFUSE_SMEM - ring) / slot;
             if (n_smem > need) n_smem = need;
             if (n_smem < 0) n_smem = 0;
-            smem = (uint32_t)(ring + n_smem * 2048);
+            smem = (uint32_t)(ring + n_smem * slot);
             size_t spill = (size_t)((need - n_smem) * ctas * k.bx * k.by * 8);
             if (spill < 256) spill = 256;
             if (spill > k.spill_bytes) {

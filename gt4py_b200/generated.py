@@ -77,7 +77,8 @@ def plan_descriptor(plan: Dict[str, Any]) -> str:
             L.append(f"{head} {k['tile'][0]} {k['tile'][1]} {k['block'][0]} {k['block'][1]} {k['smem_bytes']} "
                      f"{1 if tma else 0} {tma['smem_bytes'] if tma else 0}")
         elif k["kind"] == "colfuse":
-            L.append(f"{head} {k['block'][0]} {k['block'][1]} {k['ring_slots']} {k['stack_values_per_level']}")
+            L.append(f"{head} {k['block'][0]} {k['block'][1]} {k['ring_slots']} {k['stack_values_per_level']} "
+                     f"{k.get('stack_tmem', 128)}")
         else:
             L.append(head)
     for name, kind, ref, extra in plan["args"]:
@@ -383,10 +384,11 @@ class GeneratedStencil(StencilObject):
                 bx, by = k["block"]
                 ntiles = ((wi + bx - 1) // bx) * ((wj + by - 1) // by)
                 ctas = max(1, min(ntiles, _sm_count()))
-                need = max(0, nk * k["stack_values_per_level"] - 128)
-                ring = k["ring_slots"] * 2048
-                n_smem = max(0, min(need, (_COLFUSE_SMEM - ring) // 2048))
-                smem = ring + n_smem * 2048
+                slot = bx * by * 8
+                need = max(0, nk * k["stack_values_per_level"] - k.get("stack_tmem", 128))
+                ring = k["ring_slots"] * slot
+                n_smem = max(0, min(need, (_COLFUSE_SMEM - ring) // slot))
+                smem = ring + n_smem * slot
                 spill = self._cf_spill(k["name"], (need - n_smem) * ctas * bx * by * 8, stream)
                 setattr(a, f"cf_{k['name']}_smem", n_smem)
                 setattr(a, f"cf_{k['name']}_spill", spill)

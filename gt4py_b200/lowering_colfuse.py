@@ -24,8 +24,15 @@ from typing import Any, Dict, List, Set, Tuple
 
 from gt4py.cartesian.gtc import common, oir
 
-BX, BY = 128, 2          # threads of a CTA along I x J (one column each)
-LEAD = int(os.environ.get("B200_COLFUSE_LEAD", "6"))  # levels the prefetch runs ahead
+# threads of a CTA along I x J (one column each) and the levels the prefetch runs ahead; tuning hooks for A/B builds
+BX, BY = (int(x) for x in os.environ.get("B200_COLFUSE_BLOCK", "128x2").split("x"))
+LEAD = int(os.environ.get("B200_COLFUSE_LEAD", "6"))
+assert (BX * BY) % 128 == 0 and BX * BY <= 1024, "a fused column CTA is a whole number of 4-warp groups"
+
+
+def tmem_values(threads: int) -> int:
+    """Doubles per thread in Tensor Memory: the threads / 128 warps of a lane quarter split its 512 columns."""
+    return (512 // (threads // 128)) // 2 // 2 * 2
 
 
 def _walk(stmts, cond=False, restricted=False):
@@ -256,6 +263,7 @@ def emit(kname: str, stencil: oir.Stencil, run: List[int], units_by_loop, block_
     gen.cf_cached = an.cached
     NP = len(an.pushed)
     pslot = {name: p for p, name in enumerate(an.pushed)}
+    T, NT = BX * BY, tmem_values(BX * BY)
 
     # ---- ring layout: slots of 256 x 8 bytes; per loop the keys are laid out from slot 0 (loops reuse the region) ----
     ring_slots = 0
@@ -317,11 +325,13 @@ def emit(kname: str, stencil: oir.Stencil, run: List[int], units_by_loop, block_
     S.append("    const int tid = (int)(threadIdx.y * blockDim.x + threadIdx.x);")
     S.append("    double *const cf_ring = reinterpret_cast<double *>(b200_smem) + tid;")
     S.append("    b200_stack cf_stk;")
-    S.append("    cf_stk.tmem = b200_stack_setup(&cf_tmem_slot);")
-    S.append(f"    cf_stk.smem = reinterpret_cast<double *>(b200_smem) + {ring_slots} * 256 + tid;")
+    S.append(f"    cf_stk.n_tmem = {NT};")
+    S.append(f"    cf_stk.cta = {T};")
+    S.append(f"    cf_stk.tmem = b200_stack_setup(&cf_tmem_slot, {NT});")
+    S.append(f"    cf_stk.smem = reinterpret_cast<double *>(b200_smem) + {ring_slots} * {T} + tid;")
     S.append(f"    cf_stk.n_smem = a.cf_{kname}_smem;")
-    S.append("    cf_stk.nthreads = (long long)gridDim.x * 256;")
-    S.append(f"    cf_stk.spill = a.cf_{kname}_spill + (long long)blockIdx.x * 256 + tid;")
+    S.append(f"    cf_stk.nthreads = (long long)gridDim.x * {T};")
+    S.append(f"    cf_stk.spill = a.cf_{kname}_spill + (long long)blockIdx.x * {T} + tid;")
     S.append(f"    const int cf_tiles_i = (a.ni + ({ihi - ilo}) + {BX - 1}) / {BX};")
     S.append(f"    const int cf_tiles = cf_tiles_i * ((a.nj + ({jhi - jlo}) + {BY - 1}) / {BY});")
     S.append("    for (int cf_tile = (int)blockIdx.x; cf_tile < cf_tiles; cf_tile += (int)gridDim.x) {")
@@ -345,8 +355,8 @@ def emit(kname: str, stencil: oir.Stencil, run: List[int], units_by_loop, block_
             name, di, dj = key
             ct = ct_of(name)
             per = 8 // size_of[ct]
-            S.append(f"            {ct} *const rg{q} = reinterpret_cast<{ct} *>(cf_ring + {t['slot']} * 256);  // {name}[{di},{dj}]")
-            gen.cf_ring[key] = (f"rg{q}", t["depth"] - 1, 256 * per)
+            S.append(f"            {ct} *const rg{q} = reinterpret_cast<{ct} *>(cf_ring + {t['slot']} * {T});  // {name}[{di},{dj}]")
+            gen.cf_ring[key] = (f"rg{q}", t["depth"] - 1, T * per)
             far = t["dkmax"] if step > 0 else t["dkmin"]
             use_guards = sorted({guards[id(h)] for _, h in t["uses"]})
             lows, highs = [], []
@@ -359,7 +369,7 @@ def emit(kname: str, stencil: oir.Stencil, run: List[int], units_by_loop, block_
             S.append(f"            const int lo{q} = {fold('min', lows)}, hi{q} = {fold('max', highs)};")
             fn = "b200_cp_async8" if size_of[ct] == 8 else "b200_cp_async4"
             issue.append(f"{{ const int lv = kv + ({step * LEAD + far}); const bool ok = ({' || '.join(use_guards)}) && "
-                         f"lv >= lo{q} && lv < hi{q}; {fn}(rg{q} + (lv & {t['depth'] - 1}) * {256 * per}, "
+                         f"lv >= lo{q} && lv < hi{q}; {fn}(rg{q} + (lv & {t['depth'] - 1}) * {T * per}, "
                          f"a.{name} + (ok ? {index_at(name, di, dj, 'lv')} : 0), ok); }}")
         lo0, hi0 = L._interval_cond(secs[0][0])
         first = f"({hi0}) - 1" if backward else f"({lo0})"
@@ -396,7 +406,7 @@ def emit(kname: str, stencil: oir.Stencil, run: List[int], units_by_loop, block_
                             "                cur_{a} = b200_stack_pop(cf_stk, {s});")
             for name in loads:
                 q = order.index((name, 0, 0))
-                S.append(f"                cur_{name} = rg{q}[(k & {table[(name, 0, 0)]['depth'] - 1}) * 256];")
+                S.append(f"                cur_{name} = rg{q}[(k & {table[(name, 0, 0)]['depth'] - 1}) * {T}];")
             for h in hs:
                 S.append(f"                if ({guards[id(h)]}) {{")
                 for d in sorted(h.declarations, key=lambda d: str(d.name)):
@@ -424,7 +434,7 @@ def emit(kname: str, stencil: oir.Stencil, run: List[int], units_by_loop, block_
         src.append(f'extern "C" __global__ void __launch_bounds__({BX * BY}, 1) {kname}{suffix}(const Args a) '
                    f"{{ {kname}_impl<{flag}>(a); }}")
     meta = {"name": kname, "kind": "colfuse", "block": [BX, BY], "i_ext": [int(ilo), int(ihi)], "j_ext": [int(jlo), int(jhi)],
-            "ring_slots": int(ring_slots), "stack_values_per_level": NP, "loops": [int(x) for x in run],
+            "ring_slots": int(ring_slots), "stack_values_per_level": NP, "stack_tmem": NT, "loops": [int(x) for x in run],
             "cached": sorted(an.cached), "pushed": list(an.pushed),
             "private": sorted(nm for nm, c in an.cached.items() if not c["store"])}
     return "\n".join(src), meta

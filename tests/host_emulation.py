@@ -83,22 +83,21 @@ static inline void b200_cp_async8(void *dst, const void *src, bool valid) { if (
 static inline void b200_cp_async4(void *dst, const void *src, bool valid) { if (valid) { emu_check_src(src, 4); memcpy(dst, src, 4); } else memset(dst, 0, 4); }
 static inline void b200_cp_commit() {}
 template <int N> static inline void b200_cp_wait() {}
-#define B200_STK_TMEM 128
-static double emu_tmem[1024][B200_STK_TMEM];
-struct b200_stack { unsigned tmem; double *smem; double *spill; int n_smem; long long nthreads; };
-static inline unsigned b200_stack_setup(unsigned *slot) { return threadIdx.y * blockDim.x + threadIdx.x; }
+static double emu_tmem[1024][256];
+struct b200_stack { unsigned tmem; double *smem; double *spill; int n_tmem; int n_smem; int cta; long long nthreads; };
+static inline unsigned b200_stack_setup(unsigned *slot, int n_tmem) { return threadIdx.y * blockDim.x + threadIdx.x; }
 static inline void b200_stack_teardown(unsigned *) {}
 static inline void b200_stack_push(const b200_stack &st, int s, double v)
 {
-    if (s < B200_STK_TMEM) emu_tmem[st.tmem][s] = v;
-    else if (s - B200_STK_TMEM < st.n_smem) st.smem[(s - B200_STK_TMEM) * 256] = v;
-    else st.spill[(long long)(s - B200_STK_TMEM - st.n_smem) * st.nthreads] = v;
+    if (s < st.n_tmem) emu_tmem[st.tmem][s] = v;
+    else if (s - st.n_tmem < st.n_smem) st.smem[(s - st.n_tmem) * st.cta] = v;
+    else st.spill[(long long)(s - st.n_tmem - st.n_smem) * st.nthreads] = v;
 }
 static inline double b200_stack_pop(const b200_stack &st, int s)
 {
-    if (s < B200_STK_TMEM) return emu_tmem[st.tmem][s];
-    if (s - B200_STK_TMEM < st.n_smem) return st.smem[(s - B200_STK_TMEM) * 256];
-    return st.spill[(long long)(s - B200_STK_TMEM - st.n_smem) * st.nthreads];
+    if (s < st.n_tmem) return emu_tmem[st.tmem][s];
+    if (s - st.n_tmem < st.n_smem) return st.smem[(s - st.n_tmem) * st.cta];
+    return st.spill[(long long)(s - st.n_tmem - st.n_smem) * st.nthreads];
 }
 static inline void b200_stack_pop2(const b200_stack &st, int s, double &v0, double &v1) { v0 = b200_stack_pop(st, s); v1 = b200_stack_pop(st, s + 1); }
 static inline void b200_stack_push2(const b200_stack &st, int s, double v0, double v1) { b200_stack_push(st, s, v0); b200_stack_push(st, s + 1, v1); }
@@ -284,8 +283,9 @@ def run(plan_dir: str, fields: dict, params: dict, origins: dict, domain, window
             bx, by = k["block"]
             ntiles = ((wi + bx - 1) // bx) * ((wj + by - 1) // by)
             ctas = max(1, min(ntiles, 3))
-            need = max(0, nk * k["stack_values_per_level"] - 128)
-            n_smem = min((need + 1) // 2, (250 * 1024 - k["ring_slots"] * 2048) // 2048)  # some in smem, the rest spilled
+            slot = bx * by * 8
+            need = max(0, nk * k["stack_values_per_level"] - k.get("stack_tmem", 128))
+            n_smem = max(0, min((need + 1) // 2, (250 * 1024 - k["ring_slots"] * slot) // slot))  # some in smem, the rest spilled
             spill = np.zeros(max(1, (need - n_smem) * ctas * bx * by), dtype=np.float64)
             keep.append(spill)
             setattr(a, f"cf_{k['name']}_smem", n_smem)

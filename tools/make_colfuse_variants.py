@@ -35,8 +35,12 @@ for name in ("vertical_advection_dycore", "tridiagonal_solver", "column_physics"
 
 
 def main():
-    leads = [int(x) for x in sys.argv[1:]] or [3, 4, 8, 10]
-    jobs = [("twokernel", {}, "fuse_columns=False")] + [(f"lead{n}", {"B200_COLFUSE_LEAD": str(n)}, "") for n in leads]
+    """tags: twokernel, and b<BX>x<BY>_l<LEAD> for every "BXxBY:LEAD" argument (default: a sweep)."""
+    specs = sys.argv[1:] or ["128x2:6", "128x2:4", "192x2:3", "192x2:4", "128x3:4", "256x2:2", "256x2:3", "128x4:3"]
+    jobs = [("twokernel", {}, "fuse_columns=False")]
+    for spec in specs:
+        block, lead = spec.split(":")
+        jobs.append((f"b{block}_l{lead}", {"B200_COLFUSE_BLOCK": block, "B200_COLFUSE_LEAD": lead}, ""))
     for tag, env, opts in jobs:
         code = CHILD % {"root": ROOT, "tag": tag, "opts": opts}
         subprocess.run([sys.executable, "-c", code], env=dict(os.environ, **env), check=True)
