@@ -13,6 +13,7 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
+#include <array>
 #include <map>
 #include <mutex>
 #include <sstream>
@@ -57,7 +58,7 @@ struct TempSpec {
     std::vector<int> data;
     int li = 0, hi = 0, lj = 0, hj = 0;
 };
-enum MemberKind { M_FIELD, M_TMAP, M_ORIGIN, M_SCALAR, M_CF_SPILL, M_CF_SMEM };
+enum MemberKind { M_FIELD, M_TMAP, M_ORIGIN, M_SCALAR, M_CF_SPILL, M_CF_SMEM, M_LEVEL };
 struct Member {
     MemberKind kind;
     std::string name, ref, kernel;  // ref: field name (tmap / origin); kernel: owning kernel (tmap / cf_*)
@@ -66,7 +67,7 @@ struct Member {
     size_t offset = 0;              // byte offset in struct Args
     int field = -1, temp = -1, scalar = -1;  // resolved indices
 };
-enum KernelKind { K_POINT, K_COLUMN, K_TILE, K_COLFUSE };
+enum KernelKind { K_POINT, K_COLUMN, K_TILE, K_COLFUSE, K_LEVEL };
 struct Kernel {
     std::string name;
     KernelKind kind;
@@ -75,6 +76,15 @@ struct Kernel {
     void *entry = nullptr, *entry_u = nullptr, *entry_t = nullptr;
     void *spill = nullptr;
     size_t spill_bytes = 0;
+    // `level` kernels: one stage of a sequential loop run level by level
+    int loop = -1, backward = 0;
+    std::vector<std::array<int, 4>> intervals;  // (start level, offset, end level, offset); level 0 = START, 1 = END
+    bool has_level(int64_t lvl, int64_t nk) const
+    {
+        for (const auto &v : intervals)
+            if (nk * v[0] + v[1] <= lvl && lvl < nk * v[2] + v[3]) return true;
+        return false;
+    }
 };
 struct Scratch {
     std::vector<void *> base;      // allocations
@@ -131,7 +141,7 @@ static void layout(Plan &p)
         }
         case M_TMAP: case M_CF_SPILL: sz = 8; al = 8; break;
         case M_ORIGIN: sz = 12; al = 4; break;
-        case M_CF_SMEM: sz = 4; al = 4; break;
+        case M_CF_SMEM: case M_LEVEL: sz = 4; al = 4; break;
         case M_SCALAR: sz = al = (size_t)dtype_size(m.dtype); break;
         }
         off = align_up(off, al);
@@ -194,6 +204,7 @@ static int parse(Plan &p, const std::string &text)
             else if (kind == "scalar") { m.kind = M_SCALAR; ls >> m.dtype; }
             else if (kind == "cf_spill") { m.kind = M_CF_SPILL; ls >> m.kernel; }
             else if (kind == "cf_smem") { m.kind = M_CF_SMEM; ls >> m.kernel; }
+            else if (kind == "level") { m.kind = M_LEVEL; }
             else return fail(B200_EINVAL, "plan descriptor: unknown member kind '%s'", kind.c_str());
             if (!ls) return fail(B200_EINVAL, "plan descriptor: bad member line '%s'", line.c_str());
             p.members.push_back(m);
@@ -203,6 +214,16 @@ static int parse(Plan &p, const std::string &text)
             ls >> k.name >> kind >> k.ilo >> k.ihi >> k.jlo >> k.jhi;
             if (kind == "point") { k.kind = K_POINT; ls >> k.rows; }
             else if (kind == "column") { k.kind = K_COLUMN; }
+            else if (kind == "level") {
+                int n = 0;
+                k.kind = K_LEVEL;
+                ls >> k.rows >> k.loop >> k.backward >> n;
+                for (int v = 0; v < n; ++v) {
+                    std::array<int, 4> b{};
+                    ls >> b[0] >> b[1] >> b[2] >> b[3];
+                    k.intervals.push_back(b);
+                }
+            }
             else if (kind == "tile") { k.kind = K_TILE; ls >> k.ti >> k.tj >> k.bx >> k.by >> k.smem >> k.has_tma >> k.smem_tma; }
             else if (kind == "colfuse") { k.kind = K_COLFUSE; ls >> k.bx >> k.by >> k.ring_slots >> k.stack_values >> k.stack_tmem; }
             else return fail(B200_EINVAL, "plan descriptor: unknown kernel kind '%s'", kind.c_str());
@@ -505,6 +526,34 @@ static int launch(Plan &p, const int64_t dom[3], const b200_field *fields, int n
     for (size_t n = 0; n < p.kernels.size(); ++n) {
         Kernel &k = p.kernels[n];
         const int64_t wi = ni + k.ihi - k.ilo, wj = nj + k.jhi - k.jlo;
+        if (k.kind == K_LEVEL) {
+            // a sequential loop whose stages exchange values horizontally: `for k: for stage: all ij` -- the stages are
+            // the consecutive `level` kernels of one loop id, each launched on one level (member `lvl`) at a time
+            size_t end = n;
+            while (end < p.kernels.size() && p.kernels[end].kind == K_LEVEL && p.kernels[end].loop == k.loop) ++end;
+            size_t off_lvl = 0;
+            for (Member &m : p.members) if (m.kind == M_LEVEL) off_lvl = m.offset;
+            std::vector<char> noted(end - n, 0);
+            for (int64_t t = 0; t < nk; ++t) {
+                const int64_t lvl = k.backward ? nk - 1 - t : t;
+                for (size_t g = n; g < end; ++g) {
+                    Kernel &s = p.kernels[g];
+                    const int64_t gi = ni + s.ihi - s.ilo, gj = nj + s.jhi - s.jlo, rows = 4 * (int64_t)s.rows;
+                    if (gi <= 0 || gj <= 0 || !s.has_level(lvl, nk)) continue;
+                    uint32_t grid[3] = {(uint32_t)((gi + 63) / 64), (uint32_t)((gj + rows - 1) / rows), 1}, block[3] = {64, 4, 1};
+                    put<int32_t>(p, off_lvl, (int32_t)lvl);
+                    if (!noted[g - n]) {
+                        noted[g - n] = 1;
+                        if (!p.last_entries.empty()) p.last_entries += ",";
+                        p.last_entries += s.name + (unit ? "_u" : "");
+                    }
+                    int rc = b200_launch(unit ? s.entry_u : s.entry, grid, block, 0, stream, argp, 1);
+                    if (rc) return rc;
+                }
+            }
+            n = end - 1;
+            continue;
+        }
         if (wi <= 0 || wj <= 0) continue;
         uint32_t grid[3], block[3], smem = 0;
         void *entry = unit ? k.entry_u : k.entry;

@@ -72,6 +72,9 @@ def plan_descriptor(plan: Dict[str, Any]) -> str:
         head = f"kernel {k['name']} {k['kind']} {k['i_ext'][0]} {k['i_ext'][1]} {k['j_ext'][0]} {k['j_ext'][1]}"
         if k["kind"] == "point":
             L.append(f"{head} {int(k.get('rows_per_thread', 1))}")
+        elif k["kind"] == "level":  # rows, loop id, direction, the K intervals (0 = START / 1 = END, offset) x 2
+            iv = "".join(f" {a} {b} {c} {d}" for a, b, c, d in k["intervals"])
+            L.append(f"{head} {int(k.get('rows_per_thread', 1))} {k['loop']} {int(k['backward'])} {len(k['intervals'])}{iv}")
         elif k["kind"] == "tile":
             tma = k.get("tma")
             L.append(f"{head} {k['tile'][0]} {k['tile'][1]} {k['block'][0]} {k['block'][1]} {k['smem_bytes']} "
@@ -90,6 +93,8 @@ def plan_descriptor(plan: Dict[str, Any]) -> str:
             L.append(f"member origin {name} {ref}")
         elif kind in ("cf_spill", "cf_smem"):
             L.append(f"member {kind} {name} {ref}")
+        elif kind == "level":
+            L.append(f"member level {name}")
         else:
             L.append(f"member scalar {name} {code[ref]}")
     lib = plan.get("library")
@@ -129,7 +134,7 @@ def _args_struct(plan):
             fields.append((name, ctypes.c_int32 * 3))
         elif kind == "cf_spill":
             fields.append((name, c_void_p))
-        elif kind == "cf_smem":
+        elif kind in ("cf_smem", "level"):
             fields.append((name, ctypes.c_int32))
         else:
             fields.append((name, _CT[dtype]))
@@ -364,9 +369,30 @@ class GeneratedStencil(StencilObject):
         cls._last_entry_points = []  # what the last call launched (tests check that the intended variant ran)
         argp = (c_void_p * 1)(ctypes.cast(byref(a), c_void_p))
         sh = _lib.stream_handle(stream)
-        for k in cls._plan_["kernels"]:
+        kernels = cls._plan_["kernels"]
+        for n, k in enumerate(kernels):
             wi = ni + k["i_ext"][1] - k["i_ext"][0]
             wj = nj + k["j_ext"][1] - k["j_ext"][0]
+            if k["kind"] == "level":
+                # a sequential loop run level by level: its stages are consecutive `level` kernels of one loop id
+                if n and kernels[n - 1]["kind"] == "level" and kernels[n - 1]["loop"] == k["loop"]:
+                    continue  # launched with the head of its group
+                group = [g for g in kernels[n:] if g["kind"] == "level" and g["loop"] == k["loop"]]
+                sfx = "_u" if unit else ""
+                for lvl in level_order(nk, k["backward"]):
+                    for g in group:
+                        gi = ni + g["i_ext"][1] - g["i_ext"][0]
+                        gj = nj + g["j_ext"][1] - g["j_ext"][0]
+                        if gi <= 0 or gj <= 0 or not level_in(g["intervals"], lvl, nk):
+                            continue
+                        rows = 4 * int(g.get("rows_per_thread", 1))
+                        a.lvl = lvl
+                        if g["name"] + sfx not in cls._last_entry_points:
+                            cls._last_entry_points.append(g["name"] + sfx)
+                        _lib.check(_lib.lib().b200_launch(
+                            mod.kernels[g["name"] + sfx], (ctypes.c_uint32 * 3)((gi + 63) // 64, (gj + rows - 1) // rows, 1),
+                            (ctypes.c_uint32 * 3)(64, 4, 1), 0, sh, argp, 1))
+                continue
             if wi <= 0 or wj <= 0:
                 continue
             smem, sfx = 0, ("_u" if unit else "")
@@ -401,6 +427,16 @@ class GeneratedStencil(StencilObject):
             cls._last_entry_points.append(k["name"] + sfx)
             _lib.check(_lib.lib().b200_launch(mod.kernels[k["name"] + sfx], (ctypes.c_uint32 * 3)(*grid),
                                               (ctypes.c_uint32 * 3)(*block), smem, sh, argp, 1))
+
+
+def level_order(nk: int, backward: bool):
+    return range(nk - 1, -1, -1) if backward else range(nk)
+
+
+def level_in(intervals, lvl: int, nk: int) -> bool:
+    """Is level `lvl` inside one of a `level` kernel's K intervals ([start level, offset, end level, offset]; level
+    0 = START, 1 = END)?  (The kernel checks again; this only saves the launch.)"""
+    return any((nk * sl + so) <= lvl < (nk * el + eo) for sl, so, el, eo in intervals)
 
 
 _PY_LAUNCH = os.environ.get("B200_PY_LAUNCH", "0") == "1"

@@ -409,7 +409,7 @@ def emit(kname: str, stencil: oir.Stencil, run: List[int], units_by_loop, block_
                 S.append(f"                cur_{name} = rg{q}[(k & {table[(name, 0, 0)]['depth'] - 1}) * {T}];")
             for h in hs:
                 S.append(f"                if ({guards[id(h)]}) {{")
-                for d in sorted(h.declarations, key=lambda d: str(d.name)):
+                for d in L._declarations(h):
                     S.append(" " * 20 + f"{L.CTYPES[d.dtype]} {d.name} = 0;")
                 S += gen.stmts(h.body, 20)
                 S.append("                }")

@@ -76,3 +76,31 @@ def column_physics(t: F64, q: F64, w: F64, t_out: F64, *, dt: np.float64):
 
 
 DEFINITIONS = {"fv3_chain": (fv3_chain, {}), "column_physics": (column_physics, {})}
+
+
+def seq_exchange(a: F64, b: F64, out: F64):
+    """A sequential loop whose stages exchange values horizontally inside a level: `tmp` is written, then read at
+    I / J offsets by the next statement of the SAME level, while `out` of level k-1 feeds level k.  The reference
+    evaluates `for k: for stage: all ij` (gtc/numpy/npir_codegen.py:281-296); the b200 lowering runs the stages as
+    per-level launches.  (The frontend only admits the pattern for a temporary that lives in ONE interval block and
+    does not depend on a written API field: gtir.py:224-240, "non-zero read extent on written fields".)"""
+    with computation(FORWARD):
+        with interval(0, 1):
+            out = b
+        with interval(1, None):
+            tmp = a * b[0, 0, -1] + b
+            out = out[0, 0, -1] + 0.25 * (tmp[1, 0, 0] + tmp[-1, 0, 0] + tmp[0, 1, 0] + tmp[0, -1, 0])
+
+
+def seq_exchange_backward(a: F64, b: F64, out: F64):
+    """The BACKWARD twin of seq_exchange, with a third stage that reads the second one's result at an offset."""
+    with computation(BACKWARD):
+        with interval(-1, None):
+            out = b
+        with interval(0, -1):
+            tmp = a[0, 0, 1] * 0.5 + b
+            mid = tmp[1, 0, 0] - tmp[0, -1, 0]
+            out = out[0, 0, 1] * 0.5 + mid[-1, 0, 0] + mid[0, 1, 0] + a
+
+
+DEFINITIONS.update({"seq_exchange": (seq_exchange, {}), "seq_exchange_backward": (seq_exchange_backward, {})})

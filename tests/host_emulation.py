@@ -163,7 +163,7 @@ extern "C" void emu_{name}(const Args *a, unsigned gx, unsigned gy, unsigned gz,
 
 
 def emulable(plan) -> bool:
-    return all(k["kind"] in ("point", "column", "tile", "colfuse") for k in plan["kernels"])
+    return all(k["kind"] in ("point", "column", "tile", "colfuse", "level") for k in plan["kernels"])
 
 
 def _host_source(src: str, plan) -> str:
@@ -264,9 +264,27 @@ def run(plan_dir: str, fields: dict, params: dict, origins: dict, domain, window
                 base = arr.base if isinstance(arr.base, np.ndarray) else arr
                 lo = min(arr.ctypes.data, base.ctypes.data)
                 lib.emu_add_range(lo, max(base.nbytes, arr.nbytes))
-    for k in plan["kernels"]:  # launch geometry of generated.GeneratedStencil._launch
+    kernels = plan["kernels"]
+    for n, k in enumerate(kernels):  # launch geometry of generated.GeneratedStencil._launch
         wi = ni + k["i_ext"][1] - k["i_ext"][0]
         wj = nj + k["j_ext"][1] - k["j_ext"][0]
+        if k["kind"] == "level":  # a sequential loop run level by level: for k: for stage: all ij
+            if n and kernels[n - 1]["kind"] == "level" and kernels[n - 1]["loop"] == k["loop"]:
+                continue
+            group = [g for g in kernels[n:] if g["kind"] == "level" and g["loop"] == k["loop"]]
+            for lvl in generated.level_order(nk, k["backward"]):
+                for g in group:
+                    gi = ni + g["i_ext"][1] - g["i_ext"][0]
+                    gj = nj + g["j_ext"][1] - g["j_ext"][0]
+                    if gi <= 0 or gj <= 0 or not generated.level_in(g["intervals"], lvl, nk):
+                        continue
+                    rows = 4 * int(g.get("rows_per_thread", 1))
+                    a.lvl = lvl
+                    fn = getattr(lib, "emu_" + g["name"])
+                    fn.restype = None
+                    fn.argtypes = [ctypes.c_void_p] + [ctypes.c_uint] * 6
+                    fn(ctypes.byref(a), (gi + 63) // 64, (gj + rows - 1) // rows, 1, 64, 4, 1)
+            continue
         if wi <= 0 or wj <= 0:
             continue
         if k["kind"] == "point":

@@ -62,7 +62,7 @@ def test_plan_is_loadable_without_gt4py(name):
     cls = generated.stencil_class(plan, os.path.join(GEN, name))
     assert set(cls._gt_field_info_) | set(cls._gt_parameter_info_) == set(plan["info"]["arg_names"])
     kinds = {k["kind"] for k in plan["kernels"]}
-    assert kinds <= {"point", "column", "tile", "colfuse"}
+    assert kinds <= {"point", "column", "tile", "colfuse", "level"}
     src = open(os.path.join(GEN, name, "kernel.cu")).read()
     for k in plan["kernels"]:
         assert f" {k['name']}(const Args a)" in src and f" {k['name']}_u(const Args a)" in src
