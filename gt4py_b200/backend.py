@@ -113,6 +113,7 @@ class B200Backend(BaseBackend):
         "fuse_temporaries": {"versioning": True, "type": bool},
         "k_register_cache": {"versioning": True, "type": bool},
         "fuse_columns": {"versioning": True, "type": bool},
+        "warp_march": {"versioning": True, "type": bool},
     }
     storage_info: ClassVar[layout.LayoutInfo] = {
         "alignment": storage.ALIGNMENT,
@@ -128,10 +129,11 @@ class B200Backend(BaseBackend):
         caching = self.builder.caching
         return f"{caching.module_prefix}b200{caching.module_postfix}"
 
-    #: tile kernels (temporaries in shared memory) win over recompute-on-the-fly point kernels from about four
-    #: dependent stages on (measured at 512x512x128 on B200: lap-of-lap diffusion 0.30 vs 0.37 ms, config-4 chain
-    #: 0.57 vs 0.96 ms; but hdiff 0.31 vs 0.27 ms and 2-stage upwind advection 0.29 vs 0.23 ms)
-    AUTO_FUSE_MIN_STAGES = 4
+    #: fused kernels (temporaries in registers / shared memory) win over recompute-on-the-fly point kernels from three
+    #: dependent stages on (measured at 512x512x128 on B200, ms: hdiff point 0.227 / tile 0.240 / warp-march 0.203;
+    #: lap-of-lap diffusion 0.37 / 0.195 / 0.166; config-4 chain 0.96 / 0.393 / 0.397; two-stage upwind advection
+    #: point 0.214 / tile 0.166 when forced -- left to the point kernel by this rule, as before)
+    AUTO_FUSE_MIN_STAGES = 3
 
     @property
     def fuse(self):
@@ -171,13 +173,14 @@ class B200Backend(BaseBackend):
         name, fuse = self.builder.options.name, self.fuse
         kc = bool(self.builder.options.backend_opts.get("k_register_cache", False))
         fc = bool(self.builder.options.backend_opts.get("fuse_columns", True))
+        wm = bool(self.builder.options.backend_opts.get("warp_march", True))
         if fuse is None or fuse:
-            plan, source = lowering.lower(self.oir(True), name, fuse=True, k_register_cache=kc, fuse_columns=fc)
+            plan, source = lowering.lower(self.oir(True), name, fuse=True, k_register_cache=kc, fuse_columns=fc, warp_march=wm)
             deepest = max([k.get("stages", 0) for k in plan["kernels"]], default=0)
             if fuse is None and deepest < self.AUTO_FUSE_MIN_STAGES:
                 fuse = False
         if fuse is not None and not fuse:
-            plan, source = lowering.lower(self.oir(False), name, fuse=False, k_register_cache=kc, fuse_columns=fc)
+            plan, source = lowering.lower(self.oir(False), name, fuse=False, k_register_cache=kc, fuse_columns=fc, warp_march=wm)
         match = self.library_match()
         if match is not None:
             plan["library"] = match

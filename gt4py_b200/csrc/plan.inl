@@ -67,7 +67,7 @@ struct Member {
     size_t offset = 0;              // byte offset in struct Args
     int field = -1, temp = -1, scalar = -1;  // resolved indices
 };
-enum KernelKind { K_POINT, K_COLUMN, K_TILE, K_COLFUSE, K_LEVEL };
+enum KernelKind { K_POINT, K_COLUMN, K_TILE, K_COLFUSE, K_LEVEL, K_MARCH };
 struct Kernel {
     std::string name;
     KernelKind kind;
@@ -77,6 +77,7 @@ struct Kernel {
     void *spill = nullptr;
     size_t spill_bytes = 0;
     // `level` kernels: one stage of a sequential loop run level by level
+    int wo = 0, warps = 0, strip = 0;  // `march` kernels: result columns per warp, warps per CTA, rows per strip
     int loop = -1, backward = 0;
     std::vector<std::array<int, 4>> intervals;  // (start level, offset, end level, offset); level 0 = START, 1 = END
     bool has_level(int64_t lvl, int64_t nk) const
@@ -214,6 +215,7 @@ static int parse(Plan &p, const std::string &text)
             ls >> k.name >> kind >> k.ilo >> k.ihi >> k.jlo >> k.jhi;
             if (kind == "point") { k.kind = K_POINT; ls >> k.rows; }
             else if (kind == "column") { k.kind = K_COLUMN; }
+            else if (kind == "march") { k.kind = K_MARCH; ls >> k.wo >> k.warps >> k.strip; }
             else if (kind == "level") {
                 int n = 0;
                 k.kind = K_LEVEL;
@@ -562,6 +564,11 @@ static int launch(Plan &p, const int64_t dom[3], const b200_field *fields, int n
             const int64_t rows = 4 * (int64_t)k.rows;
             block[0] = 64; block[1] = 4; block[2] = 1;
             grid[0] = (uint32_t)((wi + 63) / 64); grid[1] = (uint32_t)((wj + rows - 1) / rows); grid[2] = (uint32_t)nk;
+        } else if (k.kind == K_MARCH) {
+            const int64_t per_cta = (int64_t)k.wo * k.warps;
+            if (per_cta <= 0 || k.strip <= 0) return fail(B200_EINVAL, "plan_launch: bad march geometry of kernel '%s'", k.name.c_str());
+            block[0] = 32u * (uint32_t)k.warps; block[1] = 1; block[2] = 1;
+            grid[0] = (uint32_t)((ni + per_cta - 1) / per_cta); grid[1] = (uint32_t)((nj + k.strip - 1) / k.strip); grid[2] = (uint32_t)nk;
         } else if (k.kind == K_TILE) {
             block[0] = (uint32_t)k.bx; block[1] = (uint32_t)k.by; block[2] = 1;
             grid[0] = (uint32_t)((ni + k.ti - 1) / k.ti); grid[1] = (uint32_t)((nj + k.tj - 1) / k.tj); grid[2] = (uint32_t)nk;

@@ -1,0 +1,313 @@
+"""Warp-march form of the fused multi-stage kernel (kernel kind ``march``).
+
+A PARALLEL vertical loop whose horizontal executions exchange temporaries at I / J offsets (the config-4 chain,
+lap-of-lap diffusion, hdiff, upwind advection) is lowered to ONE kernel in which every temporary lives in
+REGISTERS:
+
+  * a warp owns ``32 * C`` consecutive columns (C columns per lane, interleaved: lane l holds columns C*l ..
+    C*l + C - 1) of one level and marches down J over a strip of ``SJ`` rows;
+  * a temporary read at a J offset is a rolling window of rows in the lane's registers; the loop is unrolled by the
+    window period, so the window slots are plain named registers and nothing is ever shifted;
+  * a temporary read at an I offset comes from the neighbouring column of the same lane or, across lanes, by
+    ``__shfl_up/down_sync`` -- no shared memory, no ``__syncthreads()``: warps are independent;
+  * the stages are software-pipelined along J: stage s works ``L_s`` rows behind the front, with L_s the smallest
+    lag that makes every row it reads available; the read-only API inputs are pseudo-stages at the front whose rows
+    are loaded ``PREFETCH`` iterations before their first use (each input element is loaded once per warp);
+  * the halo of the extent analysis (passes/oir_optimizations/utils.py:293-330) is recomputed per warp in I (58 of
+    64 columns are results for a total I halo of 6) and per strip in J.
+
+The tile kernel of lowering._tile_kernel (a CTA per 64 x 16 tile, temporaries in shared memory, a barrier per stage) was
+bound by shared-memory traffic: 0.41 of the HBM roofline on the config-4 chain; this form trades it for shuffles and
+registers.  Counterpart in the reference: the IJ caches of the GridTools backends
+(gtc/passes/oir_optimizations/caches.py, IJCacheDetection) -- there a per-block shared-memory tile, here registers.
+
+Measured on B200 at 512 x 512 x 128 float64 (tools/make_march_variants.py + tools/chain_bench.py,
+profiles/r2_march_variants.jsonl), ms per call, tile kernel -> this form with the defaults below (one column per lane,
+4 warps per CTA, at most 80 registers): lap-of-lap diffusion 0.195 -> 0.166, hdiff 0.240 -> 0.203, config-4 chain
+0.393 -> 0.397 (a tie: 6.5 warp instructions per point against 10.3, but 10-20 resident warps per SM against 43 and
+43 % issue utilisation: bound by instruction latency, not by memory), two-stage upwind advection 0.166 -> 0.189 (the
+tile kernel is at the HBM roofline there).  Hence: used from three stages on (MIN_STAGES), two columns per lane
+(158 registers) and deeper prefetch measured slower.
+
+Not every unit qualifies (`emit` returns None and the tile kernel is used): every fused temporary must be written in
+ONE stage and read only by later stages (or at zero offset inside its own).
+"""
+from __future__ import annotations
+
+import os
+from typing import Any, Dict, List, Optional, Set, Tuple
+
+from gt4py.cartesian.gtc import common, oir
+from gt4py.cartesian.gtc.passes.oir_optimizations.utils import AccessCollector
+
+def _knob(name: str, default: int) -> int:
+    """Tuning knobs, read when a kernel is emitted (experiments and tests set them; the plan records what was used)."""
+    return int(os.environ.get(name, str(default)))
+
+
+MAX_PERIOD = 8
+MIN_STAGES = 3
+
+
+def _pow2(n: int) -> int:
+    p = 1
+    while p < n:
+        p *= 2
+    return p
+
+
+def _field_accesses(h):
+    """[(name, di, dj, dk or None, is_write)] of a horizontal execution (static Cartesian offsets; dk None: variable)."""
+    out = []
+    for a in AccessCollector.apply(h).ordered_accesses():
+        out.append((str(a.field), int(a.offset[0]), int(a.offset[1]), a.offset[2], bool(a.is_write)))
+    return out
+
+
+def emit(kname: str, unit, block_ext, fields, field_ext, scalar_names, locals_, smem_names, L
+         ) -> Optional[Tuple[str, Dict[str, Any]]]:
+    """(CUDA source, launch metadata) of the warp-march kernel of `unit`, or None if the unit does not qualify.
+    `L` is the lowering module (ExprGen, CTYPES, helpers)."""
+    C = _knob("B200_MARCH_COLUMNS", 1)          # columns per lane
+    STRIP = _knob("B200_MARCH_STRIP", 64)       # rows a warp marches over
+    PREFETCH = _knob("B200_MARCH_PREFETCH", 2)  # iterations between an input row's load and its first use
+    WARPS = _knob("B200_MARCH_WARPS", 4)        # warps per CTA (independent of each other: scheduling granularity only)
+    MINB = _knob("B200_MARCH_MIN_BLOCKS", 6)    # __launch_bounds__ second argument (caps the registers per thread: 80)
+    RUNPTR = _knob("B200_MARCH_RUNNING_POINTERS", 1)
+    stages = L._tile_stages(unit, smem_names)
+    temps = {str(x) for x in smem_names}
+    readonly = L._readonly_globals(unit, smem_names, fields)
+    stage_of: Dict[int, int] = {}
+    for n, stage in enumerate(stages):
+        for _, h in stage:
+            stage_of[id(h)] = n
+    # ---- who writes / reads what, where -------------------------------------------------------------------------
+    writer: Dict[str, int] = {}
+    reads: Dict[str, List[Tuple[int, int, int]]] = {}      # temp or staged input -> [(stage, di, dj)]
+    bad_input: Set[str] = set()
+    for n, stage in enumerate(stages):
+        for _, h in stage:
+            for name, di, dj, dk, is_write in _field_accesses(h):
+                if name in temps:
+                    if dk is None or int(dk) != 0:
+                        return None
+                    if is_write:
+                        if writer.setdefault(name, n) != n or di or dj:
+                            return None
+                    else:
+                        reads.setdefault(name, []).append((n, di, dj))
+                elif name in readonly:
+                    f = fields[name]
+                    if not all(f["dims"]) or f["data_dims"] or dk is None or int(dk) != 0:
+                        bad_input.add(name)
+                    else:
+                        reads.setdefault(name, []).append((n, di, dj))
+    for name in temps:
+        if name not in writer:
+            return None
+        for n, di, dj in reads.get(name, []):
+            if n < writer[name] or (n == writer[name] and (di or dj)):
+                return None
+    inputs = sorted(n for n in reads if n not in temps and n not in bad_input)
+    # registers that never leave one stage of one thread (no offset reads, one stage): plain locals
+    regs = {t for t in temps if all(n == writer[t] and not di and not dj for n, di, dj in reads.get(t, []))}
+    windows = sorted(temps - regs)
+    # ---- lags: stage s works on row (front - lag[s]); inputs are at the front (lag 0) ------------------------------------
+    lag = [0] * len(stages)
+    for n in range(len(stages)):
+        need = 0
+        for name in inputs:
+            for s, di, dj in reads[name]:
+                if s == n:
+                    need = max(need, PREFETCH + dj)
+        for name in windows:
+            for s, di, dj in reads[name]:
+                if s == n and writer[name] != n:
+                    need = max(need, lag[writer[name]] + max(dj, 0))
+        lag[n] = max(need, 0)
+    depth: Dict[str, int] = {}
+    for name in inputs:
+        depth[name] = _pow2(max(lag[s] - dj for s, di, dj in reads[name]) + 1)
+    for name in windows:
+        depth[name] = _pow2(max([lag[s] - dj - lag[writer[name]] for s, di, dj in reads[name]] + [0]) + 1)
+    U = max(list(depth.values()) + [1])
+    if U > MAX_PERIOD:
+        return None
+    if len(stages) < MIN_STAGES and os.environ.get("B200_MARCH", "1") != "force":
+        return None  # measured (module docstring): two-stage kernels are faster as shared-memory tile kernels
+    # ---- geometry -------------------------------------------------------------------------------------------------------------
+    exts = {id(h): block_ext[id(h)] for _, h in unit}
+    s_ext = []
+    for stage in stages:
+        es = [exts[id(h)] for _, h in stage]
+        s_ext.append((min(e[0][0] for e in es), max(e[0][1] for e in es), min(e[1][0] for e in es), max(e[1][1] for e in es)))
+    in_ext = {}
+    for name in inputs:  # the columns / rows of an input some stage may read
+        lo_i = min(s_ext[s][0] + di for s, di, dj in reads[name])
+        hi_i = max(s_ext[s][1] + di for s, di, dj in reads[name])
+        lo_j = min(s_ext[s][2] + dj for s, di, dj in reads[name])
+        hi_j = max(s_ext[s][3] + dj for s, di, dj in reads[name])
+        fe = field_ext.get(name)
+        if fe is not None:  # (mask-aware: an access inside a horizontal region does not widen the field everywhere)
+            lo_i, hi_i = max(lo_i, int(fe[0][0])), min(hi_i, int(fe[0][1]))
+            lo_j, hi_j = max(lo_j, int(fe[1][0])), min(hi_j, int(fe[1][1]))
+        in_ext[name] = (lo_i, hi_i, lo_j, hi_j)
+    ILO = min([e[0] for e in s_ext] + [e[0] for e in in_ext.values()])
+    IHI = max([e[1] for e in s_ext] + [e[1] for e in in_ext.values()])
+    ILOa = -((-ILO + C - 1) // C * C)                  # first column of lane 0, relative to the warp's first result
+    WO = 32 * C - (IHI - ILOa)                          # result columns per warp
+    if WO < 8 * C:
+        return None
+    R0 = min([s_ext[n][2] + lag[n] for n in range(len(stages))] + [e[2] for e in in_ext.values()])
+    NIT = max([STRIP + s_ext[n][3] - R0 + lag[n] for n in range(len(stages))] + [STRIP + e[3] - R0 for e in in_ext.values()])
+    NIT = (NIT + U - 1) // U * U
+    XR = max([s_ext[n][3] + lag[n] for n in range(len(stages))] + [e[3] for e in in_ext.values()])
+
+    gen = L.ExprGen(fields, scalar_names, locals_, False, regs=regs)
+    gen.readonly = readonly
+    ctype = {n: L.CTYPES[fields[n]["dtype"]] for n in list(temps) + inputs}
+
+    has_while = any(isinstance(node, oir.While) for _, h in unit for node in h.walk_values())
+    # horizontal executions that touch global memory themselves (a write to an API field, a read of a field that is not
+    # kept in register windows): they keep their guard everywhere; the others only produce register values, which a
+    # lane or row outside the execution's range may compute freely -- nothing valid ever reads them
+    touches_global = {}
+    for _, h in unit:
+        names = {nm for nm, *_ in _field_accesses(h)}
+        touches_global[id(h)] = bool(names - temps - set(inputs))
+
+    S: List[str] = []
+    S.append("    const int lane = (int)(threadIdx.x & 31u);")
+    S.append(f"    const int ic0 = ((int)blockIdx.x * {WARPS} + (int)(threadIdx.x >> 5)) * {WO};  // the warp's first result column")
+    S.append(f"    const int x0 = lane * {C} + ({ILOa});                 // this lane's first column, relative to ic0")
+    S.append(f"    const int tj0 = (int)blockIdx.y * {STRIP}, k = (int)blockIdx.z;")
+    S.append("    if (ic0 >= a.ni) return;  // (the whole warp: no lane is left behind at a shuffle)")
+    # iterations of this strip: none once every stage is past the last row it computes (a short last strip)
+    S.append(f"    const int nit = min({NIT}, a.nj + ({XR}) - (tj0 + ({R0})));")
+    for name in inputs + windows:
+        for q in range(depth[name]):
+            S.append(f"    {ctype[name]} " + ", ".join(f"w_{name}_{q}_{c} = 0" for c in range(C)) + ";")
+    # Input rows are loaded without a column guard: a lane whose column lies outside the range the stencil reads
+    # (the two halo columns beyond the warp's block, the columns past the domain's end) loads the nearest column
+    # inside it instead -- its value is never used (extent analysis), the address is always valid.
+    for name in inputs:
+        lo_i, hi_i, lo_j, hi_j = in_ext[name]
+        for c in range(C):
+            S.append(f"    const {ctype[name]} *p_{name}_{c};")
+            S.append(f"    {{ const int i = min(max(ic0 + x0 + {c}, {lo_i}), a.ni + ({hi_i}) - 1), j = 0; "
+                     f"p_{name}_{c} = g_{name} + ({gen._index(name, common.CartesianOffset.zero(), None)}); }}")
+
+    def loop(fast: bool) -> List[str]:
+        """The J march; `fast`: every column of the warp is inside the domain, and only the horizontal executions that
+        touch global memory themselves are guarded."""
+        B: List[str] = []
+        if fast and RUNPTR:
+            for name in inputs:
+                lo_i, hi_i, lo_j, hi_j = in_ext[name]
+                B.append(f"    const long long r_{name} = (long long)min(max(tj0 + ({R0}), {lo_j}), a.nj + ({hi_j}) - 1) * a.{name}_s[1];")
+                for c in range(C):
+                    B.append(f"    const {ctype[name]} *q_{name}_{c} = p_{name}_{c} + r_{name};")
+        B += ["    #pragma unroll 1", f"    for (int tb = 0; tb < nit; tb += {U}) {{"]
+        nsh = 0
+        for u in range(U):
+            B.append(f"        {{  // iteration tb + {u}")
+            B.append(f"            const int jf = tj0 + ({R0}) + tb + {u};  // the front row")
+            for name in inputs:  # input pseudo-stages: one load per (field, column) and row
+                lo_i, hi_i, lo_j, hi_j = in_ext[name]
+                q = (u % depth[name])
+                if fast and RUNPTR:
+                    # running row pointers (q_<field>_<column>, advanced by one row per iteration while inside the rows
+                    # the stencil reads; before / after them the pointer stays on the first / last such row)
+                    for c in range(C):
+                        B.append(f"            w_{name}_{q}_{c} = *q_{name}_{c};")
+                    B.append(f"            if (jf >= ({lo_j}) && jf < a.nj + ({hi_j}) - 1) {{ "
+                             + " ".join(f"q_{name}_{c} += a.{name}_s[1];" for c in range(C)) + " }")
+                    continue
+                if fast:  # a row outside the range the stencil reads: the nearest row inside it, never used
+                    B.append(f"            {{ const int jl = min(max(jf, {lo_j}), a.nj + ({hi_j}) - 1);")
+                    for c in range(C):
+                        B.append(f"                w_{name}_{q}_{c} = p_{name}_{c}[(idx_t)jl * (idx_t)a.{name}_s[1]];")
+                    B.append("            }")
+                    continue
+                B.append(f"            if (jf >= tj0 + ({lo_j}) && jf < tj0 + {STRIP} + ({hi_j}) && jf < a.nj + ({hi_j})) {{")
+                for c in range(C):
+                    B.append(f"                w_{name}_{q}_{c} = p_{name}_{c}[(idx_t)jf * (idx_t)a.{name}_s[1]];")
+                B.append("            }")
+            for n, stage in enumerate(stages):
+                ilo, ihi, jlo, jhi = s_ext[n]
+                lo, hi = L._interval_cond(stage[0][0])
+                B.append(f"            {{  // stage {n}: row front - {lag[n]}")
+                B.append(f"                const int j = jf - {lag[n]};")
+                B.append(f"                const bool row{n} = j >= tj0 + ({jlo}) && j < tj0 + {STRIP} + ({jhi}) && j < a.nj + ({jhi}) "
+                         f"&& k >= {lo} && k < {hi};")
+                # values of other lanes this stage reads: shuffled before any guard (every lane takes part)
+                shuf: Dict[Tuple[str, int, int, int], str] = {}
+                maps: List[Dict[Tuple[str, int, int], str]] = []
+                for c in range(C):
+                    m: Dict[Tuple[str, int, int], str] = {}
+                    for name in inputs + windows:
+                        for s_, di, dj in reads.get(name, []):
+                            if s_ != n:
+                                continue
+                            q = (u - lag[n] + dj) % depth[name]  # the slot of row (front - lag[n] + dj)
+                            x = c + di
+                            delta, sc = x // C, x % C
+                            if delta == 0:
+                                m[(name, di, dj)] = f"w_{name}_{q}_{sc}"
+                            else:
+                                key = (name, q, sc, delta)
+                                if key not in shuf:
+                                    shuf[key] = f"sh{nsh}"
+                                    nsh += 1
+                                    B.append(f"                const {ctype[name]} {shuf[key]} = b200_shfl(w_{name}_{q}_{sc}, {delta});")
+                                m[(name, di, dj)] = shuf[key]
+                    for name in windows:  # the stage's own output row
+                        if writer[name] == n:
+                            m[(name, 0, 0)] = f"w_{name}_{(u - lag[n]) % depth[name]}_{c}"
+                    maps.append(m)
+                for c in range(C):
+                    gen.march = maps[c]
+                    B.append(f"                {{  // column {c}")
+                    B.append(f"                    const int x = x0 + {c}, i = ic0 + x;")
+                    for name in sorted(regs):
+                        if writer[name] == n:
+                            B.append(f"                    {ctype[name]} r_{name} = 0;")
+                    for _, h in stage:
+                        e = exts[id(h)]
+                        cond = f"row{n} && x >= ({e[0][0]}) && x < {WO} + ({e[0][1]})"
+                        if not fast:
+                            cond += f" && i >= ({e[0][0]}) && i < a.ni + ({e[0][1]})"
+                        if e[1][0] != jlo:
+                            cond += f" && j >= tj0 + ({e[1][0]})"
+                        if e[1][1] != jhi:
+                            cond += f" && j < tj0 + {STRIP} + ({e[1][1]}) && j < a.nj + ({e[1][1]})"
+                        if fast and not touches_global[id(h)]:
+                            cond = "true"
+                        B.append(f"                    if ({cond}) {{")
+                        for d in L._declarations(h):
+                            B.append(" " * 24 + f"{L.CTYPES[d.dtype]} {d.name} = 0;")
+                        B += gen.stmts(h.body, 24)
+                        B.append("                    }")
+                    B.append("                }")
+                gen.march = None
+                B.append("            }")
+            B.append("        }")
+        B.append("    }")
+        return B
+
+    if has_while:  # (a `while` on a value no result depends on might not terminate)
+        S += loop(False)
+    else:
+        S.append(f"    if (ic0 + {WO} <= a.ni) {{  // every column of the warp's block is inside the domain")
+        S += ["    " + ln for ln in loop(True)]
+        S.append("    } else {")
+        S += ["    " + ln for ln in loop(False)]
+        S.append("    }")
+    all_exts = list(exts.values())
+    meta = {"name": kname, "kind": "march", "columns_per_lane": C, "strip": STRIP, "warps": WARPS, "result_columns": WO,
+            "stages": len(stages), "lags": lag, "period": U, "prefetch": PREFETCH,
+            "register_windows": {n: depth[n] for n in inputs + windows}, "register_temporaries": sorted(regs),
+            "smem_arrays": [],
+            "i_ext": [int(min(e[0][0] for e in all_exts)), int(max(e[0][1] for e in all_exts))],
+            "j_ext": [int(min(e[1][0] for e in all_exts)), int(max(e[1][1] for e in all_exts))]}
+    return L._entry_points(kname, 32 * WARPS, S, readonly, fields, MINB), meta

@@ -102,6 +102,73 @@ static inline double b200_stack_pop(const b200_stack &st, int s)
 static inline void b200_stack_pop2(const b200_stack &st, int s, double &v0, double &v1) { v0 = b200_stack_pop(st, s); v1 = b200_stack_pop(st, s + 1); }
 static inline void b200_stack_push2(const b200_stack &st, int s, double v0, double v1) { b200_stack_push(st, s, v0); b200_stack_push(st, s + 1, v1); }
 static inline void b200_stack_fence() {}
+// Warp-march kernels: the 32 lanes of a warp are fibers of ONE OS thread, resumed round-robin; a shuffle publishes the
+// lane's value and yields, so when the lane is resumed every lane has published (two buffers: a lane may already be
+// at shuffle n + 1 while others still read the values of shuffle n).  Warps of a CTA never interact: run one by one.
+#include <ucontext.h>
+static ucontext_t emu_sched, emu_lane_ctx[32];
+static int emu_cur = -1;
+static bool emu_yielded = false;
+static unsigned emu_shfl_count[32];
+static unsigned long long emu_shfl_buf[2][32];
+static inline void emu_yield() { const int me = emu_cur; emu_yielded = true; swapcontext(&emu_lane_ctx[me], &emu_sched); }
+template <typename T> static inline T b200_shfl(T v, int delta)
+{
+    const int me = emu_cur;
+    const unsigned ph = emu_shfl_count[me]++ & 1u;
+    unsigned long long raw = 0;
+    memcpy(&raw, &v, sizeof(T));
+    emu_shfl_buf[ph][me] = raw;
+    emu_yield();
+    int src = me + delta;
+    if (src < 0 || src > 31) src = me;
+    raw = emu_shfl_buf[ph][src];
+    T out;
+    memcpy(&out, &raw, sizeof(T));
+    return out;
+}
+static void emu_run_warp(void (*lane_fn)(), unsigned warp)
+{
+    const size_t STK = 512 * 1024;
+    static char *stacks = (char *)malloc(32 * STK);
+    bool alive[32];
+    for (int l = 0; l < 32; ++l) {
+        getcontext(&emu_lane_ctx[l]);
+        emu_lane_ctx[l].uc_stack.ss_sp = stacks + (size_t)l * STK;
+        emu_lane_ctx[l].uc_stack.ss_size = STK;
+        emu_lane_ctx[l].uc_link = &emu_sched;
+        makecontext(&emu_lane_ctx[l], lane_fn, 0);
+        alive[l] = true;
+        emu_shfl_count[l] = 0;
+    }
+    for (bool any = true; any;) {
+        any = false;
+        for (int l = 0; l < 32; ++l) {
+            if (!alive[l]) continue;
+            emu_cur = l;
+            threadIdx = emu_dim3{warp * 32u + (unsigned)l, 0, 0};
+            emu_yielded = false;
+            swapcontext(&emu_sched, &emu_lane_ctx[l]);
+            if (!emu_yielded) alive[l] = false; else any = true;
+        }
+    }
+    emu_cur = -1;
+}
+"""
+
+MARCH_LAUNCHER = r"""
+static const Args *emu_args_{name};
+static void emu_lane_{name}() {{ {name}(*emu_args_{name}); }}
+extern "C" void emu_{name}(const Args *a, unsigned gx, unsigned gy, unsigned gz, unsigned bx, unsigned by, unsigned bz)
+{{
+    emu_args_{name} = a;
+    blockDim = emu_dim3{{bx, by, bz}};
+    gridDim = emu_dim3{{gx, gy, gz}};
+    for (unsigned Z = 0; Z < gz; ++Z) for (unsigned Y = 0; Y < gy; ++Y) for (unsigned X = 0; X < gx; ++X) {{
+        blockIdx = emu_dim3{{X, Y, Z}};
+        for (unsigned w = 0; w < bx / 32; ++w) emu_run_warp(emu_lane_{name}, w);
+    }}
+}}
 """
 
 COLFUSE_LAUNCHER = r"""
@@ -163,7 +230,7 @@ extern "C" void emu_{name}(const Args *a, unsigned gx, unsigned gy, unsigned gz,
 
 
 def emulable(plan) -> bool:
-    return all(k["kind"] in ("point", "column", "tile", "colfuse", "level") for k in plan["kernels"])
+    return all(k["kind"] in ("point", "column", "tile", "colfuse", "level", "march") for k in plan["kernels"])
 
 
 def _host_source(src: str, plan) -> str:
@@ -180,7 +247,7 @@ def _host_source(src: str, plan) -> str:
                   "unsigned char *b200_smem = emu_smem;", body)
     out = SHIM + body
     for k in plan["kernels"]:  # the generic-stride entry point: host arrays keep numpy's strides
-        out += {"tile": TILE_LAUNCHER, "colfuse": COLFUSE_LAUNCHER}.get(k["kind"], LAUNCHER).format(name=k["name"])
+        out += {"tile": TILE_LAUNCHER, "colfuse": COLFUSE_LAUNCHER, "march": MARCH_LAUNCHER}.get(k["kind"], LAUNCHER).format(name=k["name"])
     return out
 
 
@@ -295,6 +362,11 @@ def run(plan_dir: str, fields: dict, params: dict, origins: dict, domain, window
         elif k["kind"] == "tile":
             ti, tj = k["tile"]
             block, grid = (*k["block"], 1), ((ni + ti - 1) // ti, (nj + tj - 1) // tj, nk)
+            if nk <= 0:
+                continue
+        elif k["kind"] == "march":
+            per_cta = k["result_columns"] * k["warps"]
+            block, grid = (32 * k["warps"], 1, 1), ((ni + per_cta - 1) // per_cta, (nj + k["strip"] - 1) // k["strip"], nk)
             if nk <= 0:
                 continue
         elif k["kind"] == "colfuse":  # persistent: fewer CTAs than tiles, so that the tile loop is exercised

@@ -66,7 +66,7 @@ def test_argument_validation_in_c():
 
 
 # ---- the plan-level C ABI driven from plain C (tests/abi_driver.c): b200_plan_create / launch / destroy ---------------
-def _run_c_driver(tmp_path, library, image_path, dom):
+def _run_c_driver(tmp_path, library, image_path, dom, fixture="fv3_chain"):
     import subprocess
 
     import numpy as np
@@ -75,7 +75,7 @@ def _run_c_driver(tmp_path, library, image_path, dom):
     from oracle import chain
     from oracle import inputs as gen
 
-    gen_dir = os.path.join(ROOT, "tests", "golden", "generated", "fv3_chain")
+    gen_dir = os.path.join(ROOT, "tests", "golden", "generated", fixture)
     import json
 
     with open(os.path.join(gen_dir, "plan.json")) as fh:
@@ -106,7 +106,18 @@ def test_plan_abi_from_c_on_the_host_double(tmp_path):
     image = tmp_path / "image.path"
     image.write_text(hostlib)
     out = _run_c_driver(tmp_path, emu_abi.build(), str(image), (37, 21, 4))
-    assert "entries k0_0_u" in out  # no TMA in the double: the unit-stride entry point
+    assert "entries k0_0_u" in out  # the warp-march kernel (shuffles emulated), unit-stride entry point
+
+
+def test_plan_abi_from_c_on_the_host_double_tile_kernel(tmp_path):
+    """... and on the shared-memory tile form of the chain (no TMA in the double: the unit-stride entry point)."""
+    from tests import emu_abi, host_emulation
+
+    _, hostlib = host_emulation.build_lib(os.path.join(ROOT, "tests", "golden", "generated", "fv3_chain__smem"))
+    image = tmp_path / "image.path"
+    image.write_text(hostlib)
+    out = _run_c_driver(tmp_path, emu_abi.build(), str(image), (37, 21, 4), fixture="fv3_chain__smem")
+    assert "entries k0_0_u" in out
 
 
 @pytest.mark.gpu
@@ -115,4 +126,14 @@ def test_plan_abi_from_c_on_the_gpu(tmp_path):
 
     cubin = generated.compile_cubin(os.path.join(ROOT, "tests", "golden", "generated", "fv3_chain", "kernel.cu"))
     out = _run_c_driver(tmp_path, build.build(), cubin, (200, 130, 9))
+    assert "entries k0_0_u" in out  # the warp-march kernel, unit-stride entry point
+
+
+@pytest.mark.gpu
+def test_plan_abi_from_c_on_the_gpu_tile_kernel(tmp_path):
+    """The same C program on the shared-memory tile form of the chain (backend option warp_march=False)."""
+    from gt4py_b200 import generated
+
+    cubin = generated.compile_cubin(os.path.join(ROOT, "tests", "golden", "generated", "fv3_chain__smem", "kernel.cu"))
+    out = _run_c_driver(tmp_path, build.build(), cubin, (200, 130, 9), fixture="fv3_chain__smem")
     assert "entries k0_0_t" in out  # TMA-staged entry point chosen by the plan

@@ -62,7 +62,7 @@ def test_plan_is_loadable_without_gt4py(name):
     cls = generated.stencil_class(plan, os.path.join(GEN, name))
     assert set(cls._gt_field_info_) | set(cls._gt_parameter_info_) == set(plan["info"]["arg_names"])
     kinds = {k["kind"] for k in plan["kernels"]}
-    assert kinds <= {"point", "column", "tile", "colfuse", "level"}
+    assert kinds <= {"point", "column", "tile", "colfuse", "level", "march"}
     src = open(os.path.join(GEN, name, "kernel.cu")).read()
     for k in plan["kernels"]:
         assert f" {k['name']}(const Args a)" in src and f" {k['name']}_u(const Args a)" in src
@@ -261,8 +261,9 @@ def test_library_kernel_selected_by_fingerprint_matches_too(name):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("fixture", ["fv3_chain", "fv3_chain__smem"])  # warp-march form / shared-memory tile form
 @pytest.mark.parametrize("domain", [(64, 48, 5), (130, 67, 9), (257, 129, 3)])
-def test_fv3_chain_against_the_oracle_at_other_sizes(domain):
+def test_fv3_chain_against_the_oracle_at_other_sizes(domain, fixture):
     from gt4py_b200 import storage
     from oracle import chain
 
@@ -273,18 +274,20 @@ def test_fv3_chain_against_the_oracle_at_other_sizes(domain):
     u = rng.uniform(-1.0, 1.0, phi.shape)
     v = rng.uniform(-1.0, 1.0, phi.shape)
     want = chain.fv3_chain(phi, u, v, 0.05, 0.03)
-    st = generated.load_plan(os.path.join(GEN, "fv3_chain"))
+    st = generated.load_plan(os.path.join(GEN, fixture))
     d = {k: storage.from_array(a, aligned_index=(h, h, 0)) for k, a in (("phi", phi), ("u", u), ("v", v))}
     out = storage.zeros((ni, nj, nk))
     st(d["phi"], d["u"], d["v"], out, dt=0.05, alpha=0.03, origin={"_all_": (h, h, 0), "out": (0, 0, 0)}, domain=domain)
     assert np.array_equal(out.asnumpy(), want)
-    assert type(st)._last_entry_points == ["k0_0_t"]  # the TMA-staged entry point (odd halo: base 8 bytes off)
+    # tile form: the TMA-staged entry point (odd halo: base 8 bytes off); warp-march form: unit stride
+    assert type(st)._last_entry_points == ["k0_0_t" if fixture.endswith("__smem") else "k0_0_u"]
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("mode", ["tma", "unit", "generic"])
+@pytest.mark.parametrize("mode", ["tma", "unit", "generic", "march_unit", "march_generic"])
 def test_fv3_chain_entry_points_agree(mode, monkeypatch):
-    """the three entry points of the tile kernel (<k>_t TMA-staged, <k>_u unit stride, <k> any strides)"""
+    """the three entry points of the tile kernel (<k>_t TMA-staged, <k>_u unit stride, <k> any strides) and the two of
+    the warp-march kernel"""
     from gt4py_b200 import storage
     from oracle import chain
 
@@ -295,8 +298,8 @@ def test_fv3_chain_entry_points_agree(mode, monkeypatch):
     want = chain.fv3_chain(host["phi"], host["u"], host["v"], 0.05, 0.03)
     if mode == "unit":
         monkeypatch.setenv("B200_GENERATED_TMA", "0")
-    st = generated.load_plan(os.path.join(GEN, "fv3_chain"))
-    if mode == "generic":  # K-fastest storage viewed as (I, J, K): stride_I != 1
+    st = generated.load_plan(os.path.join(GEN, "fv3_chain" if mode.startswith("march") else "fv3_chain__smem"))
+    if mode.endswith("generic"):  # K-fastest storage viewed as (I, J, K): stride_I != 1
         d = {k: storage.from_array(np.ascontiguousarray(a.transpose(2, 1, 0))).transpose(2, 1, 0) for k, a in host.items()}
     else:
         d = {k: storage.from_array(a, aligned_index=(h, h, 0)) for k, a in host.items()}
@@ -307,7 +310,8 @@ def test_fv3_chain_entry_points_agree(mode, monkeypatch):
         warnings.simplefilter("ignore")  # non-optimal layout warning for the transposed fields
         st(d["phi"], d["u"], d["v"], out, dt=0.05, alpha=0.03, origin={"_all_": (h, h, 0), "out": (0, 0, 0)}, domain=domain)
     assert np.array_equal(out.asnumpy(), want)
-    assert type(st)._last_entry_points == [{"tma": "k0_0_t", "unit": "k0_0_u", "generic": "k0_0"}[mode]]
+    assert type(st)._last_entry_points == [{"tma": "k0_0_t", "unit": "k0_0_u", "generic": "k0_0", "march_unit": "k0_0_u",
+                                            "march_generic": "k0_0"}[mode]]
 
 
 # ---- CPU: the point / column lowerings executed on the host against the reference-made golden outputs --------------
@@ -367,8 +371,28 @@ _CASES += [("vertical_advection_dycore", (9, 5, 80)), ("vertical_advection_dycor
            ("vertical_advection_dycore__f32", (40, 3, 90))]
 
 
+@pytest.mark.parametrize("name,domain,knobs", [
+    ("fv3_chain", (130, 37, 2), {"B200_MARCH_STRIP": "8"}),                              # 5 warps x 5 strips
+    ("fv3_chain", (130, 21, 3), {"B200_MARCH_STRIP": "5", "B200_MARCH_COLUMNS": "2"}),   # two columns per lane
+    ("fv3_chain", (61, 19, 2), {"B200_MARCH_STRIP": "16", "B200_MARCH_PREFETCH": "0", "B200_MARCH_WARPS": "1"}),
+    ("horizontal_diffusion__tile", (120, 40, 2), {"B200_MARCH_STRIP": "8", "B200_MARCH_COLUMNS": "2"}),
+    ("exec_info_diffusion", (59, 33, 3), {"B200_MARCH_STRIP": "4", "B200_MARCH_PREFETCH": "3"}),
+    ("simple_horizontal_diffusion__tile", (63, 30, 2), {"B200_MARCH_STRIP": "8"}),
+    ("native_functions__tile", (40, 13, 2), {"B200_MARCH_STRIP": "8", "B200_MARCH": "force"}),      # two stages: forced
+    ("exec_info_advection__tile", (70, 23, 2), {"B200_MARCH_STRIP": "8", "B200_MARCH": "force", "B200_MARCH_COLUMNS": "2"}),
+    ("fv3_chain__f32", (70, 23, 2), {"B200_MARCH_STRIP": "8"}),
+])
+def test_warp_march_kernels_over_strips_and_knobs(name, domain, knobs, monkeypatch):
+    """The warp-march form (lowering_march.py) with short strips (several strips per column block, prologue rows of one
+    strip overlapping the previous one), one and two columns per lane, other prefetch distances: bit-exact against the
+    reference's numpy backend on the host-emulated kernels."""
+    for k, v in knobs.items():
+        monkeypatch.setenv(k, v)
+    test_lowering_against_the_reference_at_other_sizes(name, domain, rebuild=True, expect_kind="march")
+
+
 @pytest.mark.parametrize("name,domain", _CASES)
-def test_lowering_against_the_reference_at_other_sizes(name, domain):
+def test_lowering_against_the_reference_at_other_sizes(name, domain, rebuild=False, expect_kind=None):
     """Differential test in the build container: the reference's numpy backend and the host-emulated kernels of a
     FRESH lowering on the same seeded inputs, at sizes that cross tile / block / row-march boundaries (the
     committed golden files are all 13 x 11 x 10).  Bit-exact."""
@@ -383,7 +407,9 @@ def test_lowering_against_the_reference_at_other_sizes(name, domain):
     opts = rest[0] if rest else {}
     common = rest[1] if len(rest) > 1 else {}
     ref = gtscript.stencil("numpy", fn, externals=ext, format_source=False, name=name, **common)
-    b2 = gtscript.stencil("b200", fn, externals=ext, format_source=False, name=name, **common, **opts)
+    b2 = gtscript.stencil("b200", fn, externals=ext, format_source=False, name=name, rebuild=rebuild, **common, **opts)
+    if expect_kind is not None:
+        assert expect_kind in [k["kind"] for k in type(b2)._b200()._plan_["kernels"]]
     domain = (domain[0], domain[1], max(domain[2], ref.domain_info.min_sequential_axis_size))
     fields, params, origins = mk.make_inputs(ref, domain, seed=sum(domain) + len(name))
     want = {k: (None if v is None else v.copy()) for k, v in fields.items()}

@@ -31,9 +31,13 @@ GEN = os.path.join(HERE, "golden", "generated")
 #: fixture name -> (domain, kernel kinds expected, entry-point suffix expected of the first kernel or None)
 CASES = {
     "exec_info_advection": ((303, 201, 40), ["point"], "_u"),
-    "exec_info_diffusion": ((301, 203, 41), ["tile"], "_t"),
-    "fv3_chain": ((300, 200, 40), ["tile"], "_t"),
-    "horizontal_diffusion__tile": ((322, 197, 40), ["tile"], "_t"),
+    "exec_info_diffusion": ((301, 203, 41), ["march"], "_u"),           # warp-march form (lowering_march.py)
+    "fv3_chain": ((300, 200, 40), ["march"], "_u"),
+    "horizontal_diffusion__tile": ((322, 197, 40), ["march"], "_u"),
+    "exec_info_advection__tile": ((257, 190, 33), ["tile"], "_t"),      # two stages: the tile form is the faster one
+    "exec_info_diffusion__smem": ((301, 203, 41), ["tile"], "_t"),      # shared-memory tile form, TMA-staged inputs
+    "fv3_chain__smem": ((300, 200, 40), ["tile"], "_t"),
+    "horizontal_diffusion__smem": ((322, 197, 40), ["tile"], "_t"),
     "column_physics": ((300, 200, 64), ["colfuse"], "_u"),          # fused FORWARD + BACKWARD (lowering_colfuse.py)
     "vertical_advection_dycore": ((300, 131, 80), ["colfuse"], "_u"),  # lowered kernels (library matching off)
     "tridiagonal_solver": ((257, 66, 80), ["colfuse"], "_u"),
@@ -143,7 +147,7 @@ def test_fv3_chain_at_baseline_config_3():
         storage.fill_synthetic(f[name], seed, -1.0, 1.5, global_offset=(-h, -h))
     out = storage.zeros(dom)
     st(f["phi"], f["u"], f["v"], out, dt=0.05, alpha=0.03, origin={"_all_": (h, h, 0), "out": (0, 0, 0)}, domain=dom)
-    assert type(st)._last_entry_points == ["k0_0_t"]
+    assert type(st)._last_entry_points == ["k0_0_u"] and st._plan_["kernels"][0]["kind"] == "march"
     levels = [0, 1, 63, 64, 127]
     host = {name: gen.hashed_window(-h, -h, dom[0] + 2 * h, dom[1] + 2 * h, dom[2], seed, -1.0, 1.5)[:, :, levels]
             for name, seed in (("phi", 91), ("u", 92), ("v", 93))}

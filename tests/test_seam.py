@@ -124,7 +124,7 @@ def body_chain():
     _run_pair(gt_storage, st_dev, st_ref, f, {"dt": 0.05, "alpha": 0.03}, (h, h, 0), CH, ["out"],
               aligned={k: (h, h, 0) for k in f})
     kinds = [k["kind"] for k in type(st_dev)._b200()._plan_["kernels"]]
-    assert kinds == ["tile"]  # one fused kernel, temporaries on chip
+    assert kinds == ["march"]  # one fused kernel, temporaries in registers
 
 
 def body_sequential_exchange():
