@@ -215,7 +215,7 @@ static int parse(Plan &p, const std::string &text)
             ls >> k.name >> kind >> k.ilo >> k.ihi >> k.jlo >> k.jhi;
             if (kind == "point") { k.kind = K_POINT; ls >> k.rows; }
             else if (kind == "column") { k.kind = K_COLUMN; }
-            else if (kind == "march") { k.kind = K_MARCH; ls >> k.wo >> k.warps >> k.strip; }
+            else if (kind == "march") { k.kind = K_MARCH; ls >> k.wo >> k.warps >> k.strip >> k.smem; }
             else if (kind == "level") {
                 int n = 0;
                 k.kind = K_LEVEL;
@@ -334,7 +334,7 @@ static int create(const char *desc, size_t desc_bytes, const void *image, size_t
         if (k.kind == K_COLFUSE) {
             rc = b200_kernel_set_smem(k.entry, B200_PLAN_COLFUSE_SMEM);
             if (!rc) rc = b200_kernel_set_smem(k.entry_u, B200_PLAN_COLFUSE_SMEM);
-        } else if (k.kind == K_TILE) {
+        } else if (k.kind == K_TILE || k.kind == K_MARCH) {
             if (k.smem > 48 * 1024) {
                 rc = b200_kernel_set_smem(k.entry, k.smem);
                 if (!rc) rc = b200_kernel_set_smem(k.entry_u, k.smem);
@@ -569,6 +569,7 @@ static int launch(Plan &p, const int64_t dom[3], const b200_field *fields, int n
             if (per_cta <= 0 || k.strip <= 0) return fail(B200_EINVAL, "plan_launch: bad march geometry of kernel '%s'", k.name.c_str());
             block[0] = 32u * (uint32_t)k.warps; block[1] = 1; block[2] = 1;
             grid[0] = (uint32_t)((ni + per_cta - 1) / per_cta); grid[1] = (uint32_t)((nj + k.strip - 1) / k.strip); grid[2] = (uint32_t)nk;
+            smem = (uint32_t)k.smem;  // the lanes' input rings
         } else if (k.kind == K_TILE) {
             block[0] = (uint32_t)k.bx; block[1] = (uint32_t)k.by; block[2] = 1;
             grid[0] = (uint32_t)((ni + k.ti - 1) / k.ti); grid[1] = (uint32_t)((nj + k.tj - 1) / k.tj); grid[2] = (uint32_t)nk;

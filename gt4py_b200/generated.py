@@ -75,8 +75,8 @@ def plan_descriptor(plan: Dict[str, Any]) -> str:
         elif k["kind"] == "level":  # rows, loop id, direction, the K intervals (0 = START / 1 = END, offset) x 2
             iv = "".join(f" {a} {b} {c} {d}" for a, b, c, d in k["intervals"])
             L.append(f"{head} {int(k.get('rows_per_thread', 1))} {k['loop']} {int(k['backward'])} {len(k['intervals'])}{iv}")
-        elif k["kind"] == "march":  # result columns per warp, warps per CTA, rows per strip
-            L.append(f"{head} {k['result_columns']} {k['warps']} {k['strip']}")
+        elif k["kind"] == "march":  # result columns per warp, warps per CTA, rows per strip, dynamic shared memory
+            L.append(f"{head} {k['result_columns']} {k['warps']} {k['strip']} {k.get('smem_bytes', 0)}")
         elif k["kind"] == "tile":
             tma = k.get("tma")
             L.append(f"{head} {k['tile'][0]} {k['tile'][1]} {k['block'][0]} {k['block'][1]} {k['smem_bytes']} "
@@ -404,6 +404,7 @@ class GeneratedStencil(StencilObject):
             elif k["kind"] == "march":  # a warp per (result columns x strip of rows) of a level (lowering_march.py)
                 per_cta = k["result_columns"] * k["warps"]
                 block, grid = (32 * k["warps"], 1, 1), ((ni + per_cta - 1) // per_cta, (nj + k["strip"] - 1) // k["strip"], nk)
+                smem = k.get("smem_bytes", 0)  # the lanes' input rings
             elif k["kind"] == "tile":  # a CTA per TI x TJ tile of the compute domain and level; halo recomputed
                 ti, tj = k["tile"]
                 block, grid, smem = (*k["block"], 1), ((ni + ti - 1) // ti, (nj + tj - 1) // tj, nk), k["smem_bytes"]

@@ -1,36 +1,41 @@
 """Warp-march form of the fused multi-stage kernel (kernel kind ``march``).
 
 A PARALLEL vertical loop whose horizontal executions exchange temporaries at I / J offsets (the config-4 chain,
-lap-of-lap diffusion, hdiff, upwind advection) is lowered to ONE kernel in which every temporary lives in
-REGISTERS:
+lap-of-lap diffusion, hdiff) is lowered to ONE kernel in which every temporary lives in REGISTERS:
 
   * a warp owns ``32 * C`` consecutive columns (C columns per lane, interleaved: lane l holds columns C*l ..
-    C*l + C - 1) of one level and marches down J over a strip of ``SJ`` rows;
+    C*l + C - 1) of one level and marches down J over a strip of ``STRIP`` rows;
   * a temporary read at a J offset is a rolling window of rows in the lane's registers; the loop is unrolled by the
     window period, so the window slots are plain named registers and nothing is ever shifted;
   * a temporary read at an I offset comes from the neighbouring column of the same lane or, across lanes, by
-    ``__shfl_up/down_sync`` -- no shared memory, no ``__syncthreads()``: warps are independent;
+    ``__shfl_up/down_sync`` -- no ``__syncthreads()``: warps are independent;
   * the stages are software-pipelined along J: stage s works ``L_s`` rows behind the front, with L_s the smallest
-    lag that makes every row it reads available; the read-only API inputs are pseudo-stages at the front whose rows
-    are loaded ``PREFETCH`` iterations before their first use (each input element is loaded once per warp);
-  * the halo of the extent analysis (passes/oir_optimizations/utils.py:293-330) is recomputed per warp in I (58 of
-    64 columns are results for a total I halo of 6) and per strip in J.
+    lag that makes every row it reads available;
+  * the read-only API inputs are copied ``LEAD`` rows ahead of the front by ``cp.async`` into a ring in shared memory
+    that is private to the lane (its own columns only: no barrier, just ``cp.async.wait_group``), each element once
+    per warp; the ring depth is the unroll period, so every slot is an immediate offset.  (A first version loaded
+    the inputs into register windows ahead of use; ncu showed half of all stall samples on the moves of those loaded
+    values -- ptxas consumed them at once -- and 43 % issue utilisation; with the ring: 76 %.)
+  * the halo of the extent analysis (passes/oir_optimizations/utils.py:293-330) is recomputed per warp in I (26 of
+    32 columns are results for a total I halo of 6) and per strip in J; a lane or row outside a stage's range
+    computes values nothing valid ever reads, so only the horizontal executions that touch global memory themselves
+    are guarded (the copies clamp their address instead).
 
-The tile kernel of lowering._tile_kernel (a CTA per 64 x 16 tile, temporaries in shared memory, a barrier per stage) was
-bound by shared-memory traffic: 0.41 of the HBM roofline on the config-4 chain; this form trades it for shuffles and
-registers.  Counterpart in the reference: the IJ caches of the GridTools backends
-(gtc/passes/oir_optimizations/caches.py, IJCacheDetection) -- there a per-block shared-memory tile, here registers.
+The tile kernel of lowering._tile_kernel (a CTA per 64 x 16 tile, temporaries in shared memory, a barrier per stage) is
+bound by shared-memory traffic and barriers on deep chains.  Counterpart in the reference: the IJ caches of the
+GridTools backends (gtc/passes/oir_optimizations/caches.py, IJCacheDetection) -- there a per-block shared-memory tile,
+here registers.
 
 Measured on B200 at 512 x 512 x 128 float64 (tools/make_march_variants.py + tools/chain_bench.py,
-profiles/r2_march_variants.jsonl), ms per call, tile kernel -> this form with the defaults below (one column per lane,
-4 warps per CTA, at most 80 registers): lap-of-lap diffusion 0.195 -> 0.166, hdiff 0.240 -> 0.203, config-4 chain
-0.393 -> 0.397 (a tie: 6.5 warp instructions per point against 10.3, but 10-20 resident warps per SM against 43 and
-43 % issue utilisation: bound by instruction latency, not by memory), two-stage upwind advection 0.166 -> 0.189 (the
-tile kernel is at the HBM roofline there).  Hence: used from three stages on (MIN_STAGES), two columns per lane
-(158 registers) and deeper prefetch measured slower.
+profiles/r2_march_variants*.jsonl), ms per call, tile kernel -> this form with the defaults below (one column per lane,
+4 warps per CTA, 80 registers, LEAD 2): config-4 chain 0.393 -> 0.322, lap-of-lap diffusion 0.195 -> 0.160, hdiff
+0.240 -> 0.174; two-stage upwind advection stays a tile kernel (0.163, at the HBM roofline; this form: 0.19).  It is
+now bound by instruction issue (7.6 warp instructions per point on the chain, of which 1.4 are float64 arithmetic):
+two columns per lane halve the shuffles but need 128 registers and measured slower (0.395 on the chain).
 
 Not every unit qualifies (`emit` returns None and the tile kernel is used): every fused temporary must be written in
-ONE stage and read only by later stages (or at zero offset inside its own).
+ONE stage and read only by later stages (or at zero offset inside its own), and the kernel must have at least
+MIN_STAGES stages.
 """
 from __future__ import annotations
 
@@ -70,10 +75,9 @@ def emit(kname: str, unit, block_ext, fields, field_ext, scalar_names, locals_, 
     `L` is the lowering module (ExprGen, CTYPES, helpers)."""
     C = _knob("B200_MARCH_COLUMNS", 1)          # columns per lane
     STRIP = _knob("B200_MARCH_STRIP", 64)       # rows a warp marches over
-    PREFETCH = _knob("B200_MARCH_PREFETCH", 2)  # iterations between an input row's load and its first use
+    LEAD = _knob("B200_MARCH_LEAD", 2)          # rows an input is copied into the lane's shared-memory ring ahead of use
     WARPS = _knob("B200_MARCH_WARPS", 4)        # warps per CTA (independent of each other: scheduling granularity only)
-    MINB = _knob("B200_MARCH_MIN_BLOCKS", 6)    # __launch_bounds__ second argument (caps the registers per thread: 80)
-    RUNPTR = _knob("B200_MARCH_RUNNING_POINTERS", 1)
+    MINB = _knob("B200_MARCH_MIN_BLOCKS", 0)    # __launch_bounds__ second argument (caps the registers per thread)
     stages = L._tile_stages(unit, smem_names)
     temps = {str(x) for x in smem_names}
     readonly = L._readonly_globals(unit, smem_names, fields)
@@ -98,7 +102,8 @@ def emit(kname: str, unit, block_ext, fields, field_ext, scalar_names, locals_, 
                         reads.setdefault(name, []).append((n, di, dj))
                 elif name in readonly:
                     f = fields[name]
-                    if not all(f["dims"]) or f["data_dims"] or dk is None or int(dk) != 0:
+                    if (not all(f["dims"]) or f["data_dims"] or dk is None or int(dk) != 0
+                            or L.CTYPES[f["dtype"]] not in L.TMA_DTYPES):  # (4 / 8 bytes: what cp.async copies)
                         bad_input.add(name)
                     else:
                         reads.setdefault(name, []).append((n, di, dj))
@@ -119,15 +124,13 @@ def emit(kname: str, unit, block_ext, fields, field_ext, scalar_names, locals_, 
         for name in inputs:
             for s, di, dj in reads[name]:
                 if s == n:
-                    need = max(need, PREFETCH + dj)
+                    need = max(need, dj)
         for name in windows:
             for s, di, dj in reads[name]:
                 if s == n and writer[name] != n:
                     need = max(need, lag[writer[name]] + max(dj, 0))
         lag[n] = max(need, 0)
     depth: Dict[str, int] = {}
-    for name in inputs:
-        depth[name] = _pow2(max(lag[s] - dj for s, di, dj in reads[name]) + 1)
     for name in windows:
         depth[name] = _pow2(max([lag[s] - dj - lag[writer[name]] for s, di, dj in reads[name]] + [0]) + 1)
     U = max(list(depth.values()) + [1])
@@ -162,6 +165,22 @@ def emit(kname: str, unit, block_ext, fields, field_ext, scalar_names, locals_, 
     NIT = max([STRIP + s_ext[n][3] - R0 + lag[n] for n in range(len(stages))] + [STRIP + e[3] - R0 for e in in_ext.values()])
     NIT = (NIT + U - 1) // U * U
     XR = max([s_ext[n][3] + lag[n] for n in range(len(stages))] + [e[3] for e in in_ext.values()])
+    # per-lane input rings in shared memory: rows front - back .. front + LEAD of the lane's own columns
+    back = max([lag[s_] - dj for name in inputs for s_, di, dj in reads[name]] + [0])
+    RD = _pow2(LEAD + back + 1)
+    T = 32 * WARPS
+    # with the loop unrolled by a multiple of the ring depth every ring slot is a compile-time offset (an immediate in
+    # the LDS / cp.async address) instead of three integer instructions per access
+    STATIC = _knob("B200_MARCH_STATIC_SLOTS", 1) and max(U, RD) <= MAX_PERIOD
+    if STATIC:
+        U = max(U, RD)
+        NIT = (NIT + U - 1) // U * U
+    ring_off: Dict[Tuple[str, int], int] = {}
+    smem_bytes = 0
+    for name in inputs:
+        for c in range(C):
+            ring_off[(name, c)] = smem_bytes
+            smem_bytes += RD * T * L.TMA_DTYPES[L.CTYPES[fields[name]["dtype"]]]
 
     gen = L.ExprGen(fields, scalar_names, locals_, False, regs=regs)
     gen.readonly = readonly
@@ -184,10 +203,15 @@ def emit(kname: str, unit, block_ext, fields, field_ext, scalar_names, locals_, 
     S.append("    if (ic0 >= a.ni) return;  // (the whole warp: no lane is left behind at a shuffle)")
     # iterations of this strip: none once every stage is past the last row it computes (a short last strip)
     S.append(f"    const int nit = min({NIT}, a.nj + ({XR}) - (tj0 + ({R0})));")
-    for name in inputs + windows:
+    for name in windows:
         for q in range(depth[name]):
             S.append(f"    {ctype[name]} " + ", ".join(f"w_{name}_{q}_{c} = 0" for c in range(C)) + ";")
-    # Input rows are loaded without a column guard: a lane whose column lies outside the range the stencil reads
+    if inputs:
+        S.append("    extern __shared__ __align__(16) unsigned char b200_smem[];")
+    for name in inputs:  # slot s of this lane's ring: rg_<field>_<column>[s * T]
+        for c in range(C):
+            S.append(f"    {ctype[name]} *rg_{name}_{c} = ({ctype[name]} *)(b200_smem + {ring_off[(name, c)]}) + (int)threadIdx.x;")
+    # Input rows are copied without a column guard: a lane whose column lies outside the range the stencil reads
     # (the two halo columns beyond the warp's block, the columns past the domain's end) loads the nearest column
     # inside it instead -- its value is never used (extent analysis), the address is always valid.
     for name in inputs:
@@ -200,39 +224,37 @@ def emit(kname: str, unit, block_ext, fields, field_ext, scalar_names, locals_, 
     def loop(fast: bool) -> List[str]:
         """The J march; `fast`: every column of the warp is inside the domain, and only the horizontal executions that
         touch global memory themselves are guarded."""
-        B: List[str] = []
-        if fast and RUNPTR:
+        def issue(row: str, slot_const: int, ind: int) -> List[str]:
+            """cp.async of row `row` of every input (clamped to the rows the stencil reads: a row outside them is never
+            used, the address is always valid) into ring slot (tb + slot_const) mod RD"""
+            out = []
+            sl = f"((tb + ({slot_const})) & {RD - 1})" if not STATIC else str(slot_const % RD)
             for name in inputs:
                 lo_i, hi_i, lo_j, hi_j = in_ext[name]
-                B.append(f"    const long long r_{name} = (long long)min(max(tj0 + ({R0}), {lo_j}), a.nj + ({hi_j}) - 1) * a.{name}_s[1];")
+                cp = "b200_cp_async8" if L.TMA_DTYPES[ctype[name]] == 8 else "b200_cp_async4"
+                out.append(" " * ind + f"{{ const int jl = min(max({row}, {lo_j}), a.nj + ({hi_j}) - 1);")
                 for c in range(C):
-                    B.append(f"    const {ctype[name]} *q_{name}_{c} = p_{name}_{c} + r_{name};")
+                    out.append(" " * ind + f"  {cp}(rg_{name}_{c} + {sl} * {T}, p_{name}_{c} + (idx_t)jl * (idx_t)a.{name}_s[1], true);")
+                out.append(" " * ind + "}")
+            out.append(" " * ind + "b200_cp_commit();")
+            return out
+
+        B: List[str] = []
+        if inputs:  # the first LEAD rows
+            B.append("    { const int tb = 0;")
+            for l in range(LEAD):
+                B += issue(f"tj0 + ({R0}) + {l}", l, 6)
+            B.append("    }")
         B += ["    #pragma unroll 1", f"    for (int tb = 0; tb < nit; tb += {U}) {{"]
         nsh = 0
         for u in range(U):
             B.append(f"        {{  // iteration tb + {u}")
             B.append(f"            const int jf = tj0 + ({R0}) + tb + {u};  // the front row")
-            for name in inputs:  # input pseudo-stages: one load per (field, column) and row
-                lo_i, hi_i, lo_j, hi_j = in_ext[name]
-                q = (u % depth[name])
-                if fast and RUNPTR:
-                    # running row pointers (q_<field>_<column>, advanced by one row per iteration while inside the rows
-                    # the stencil reads; before / after them the pointer stays on the first / last such row)
-                    for c in range(C):
-                        B.append(f"            w_{name}_{q}_{c} = *q_{name}_{c};")
-                    B.append(f"            if (jf >= ({lo_j}) && jf < a.nj + ({hi_j}) - 1) {{ "
-                             + " ".join(f"q_{name}_{c} += a.{name}_s[1];" for c in range(C)) + " }")
-                    continue
-                if fast:  # a row outside the range the stencil reads: the nearest row inside it, never used
-                    B.append(f"            {{ const int jl = min(max(jf, {lo_j}), a.nj + ({hi_j}) - 1);")
-                    for c in range(C):
-                        B.append(f"                w_{name}_{q}_{c} = p_{name}_{c}[(idx_t)jl * (idx_t)a.{name}_s[1]];")
-                    B.append("            }")
-                    continue
-                B.append(f"            if (jf >= tj0 + ({lo_j}) && jf < tj0 + {STRIP} + ({hi_j}) && jf < a.nj + ({hi_j})) {{")
-                for c in range(C):
-                    B.append(f"                w_{name}_{q}_{c} = p_{name}_{c}[(idx_t)jf * (idx_t)a.{name}_s[1]];")
-                B.append("            }")
+            if inputs:
+                B += issue(f"jf + {LEAD}", u + LEAD, 12)
+                B.append(f"            b200_cp_wait<{LEAD}>();  // rows up to the front row have arrived")
+            ring_loads: Dict[Tuple[str, int, int], str] = {}   # (input, column, row - front) -> local holding it
+            top = len(B)                                        # the ring reads of the iteration go here
             for n, stage in enumerate(stages):
                 ilo, ihi, jlo, jhi = s_ext[n]
                 lo, hi = L._interval_cond(stage[0][0])
@@ -249,17 +271,24 @@ def emit(kname: str, unit, block_ext, fields, field_ext, scalar_names, locals_, 
                         for s_, di, dj in reads.get(name, []):
                             if s_ != n:
                                 continue
-                            q = (u - lag[n] + dj) % depth[name]  # the slot of row (front - lag[n] + dj)
                             x = c + di
                             delta, sc = x // C, x % C
+                            if name in inputs:  # row (front - lag[n] + dj) of the lane's ring, read once per iteration
+                                ro = dj - lag[n]
+                                if (name, sc, ro) not in ring_loads:
+                                    ring_loads[(name, sc, ro)] = f"v{u}_{name}_{sc}_{'m' if ro < 0 else 'p'}{abs(ro)}"
+                                src, q = ring_loads[(name, sc, ro)], ro
+                            else:
+                                q = (u - lag[n] + dj) % depth[name]  # the slot of row (front - lag[n] + dj)
+                                src = f"w_{name}_{q}_{sc}"
                             if delta == 0:
-                                m[(name, di, dj)] = f"w_{name}_{q}_{sc}"
+                                m[(name, di, dj)] = src
                             else:
                                 key = (name, q, sc, delta)
                                 if key not in shuf:
                                     shuf[key] = f"sh{nsh}"
                                     nsh += 1
-                                    B.append(f"                const {ctype[name]} {shuf[key]} = b200_shfl(w_{name}_{q}_{sc}, {delta});")
+                                    B.append(f"                const {ctype[name]} {shuf[key]} = b200_shfl({src}, {delta});")
                                 m[(name, di, dj)] = shuf[key]
                     for name in windows:  # the stage's own output row
                         if writer[name] == n:
@@ -291,8 +320,14 @@ def emit(kname: str, unit, block_ext, fields, field_ext, scalar_names, locals_, 
                     B.append("                }")
                 gen.march = None
                 B.append("            }")
+            loads = [f"            const {ctype[name]} {var} = rg_{name}_{sc}["
+                     + (f"((tb + ({u + ro})) & {RD - 1}) * {T}];" if not STATIC else f"{((u + ro) % RD) * T}];")
+                     for (name, sc, ro), var in ring_loads.items()]
+            B[top:top] = loads
             B.append("        }")
         B.append("    }")
+        if inputs:
+            B.append("    b200_cp_wait<0>();")
         return B
 
     if has_while:  # (a `while` on a value no result depends on might not terminate)
@@ -305,8 +340,9 @@ def emit(kname: str, unit, block_ext, fields, field_ext, scalar_names, locals_, 
         S.append("    }")
     all_exts = list(exts.values())
     meta = {"name": kname, "kind": "march", "columns_per_lane": C, "strip": STRIP, "warps": WARPS, "result_columns": WO,
-            "stages": len(stages), "lags": lag, "period": U, "prefetch": PREFETCH,
-            "register_windows": {n: depth[n] for n in inputs + windows}, "register_temporaries": sorted(regs),
+            "stages": len(stages), "lags": lag, "period": U, "lead": LEAD, "ring_rows": RD,
+            "smem_bytes": int(smem_bytes), "input_rings": inputs,
+            "register_windows": {n: depth[n] for n in windows}, "register_temporaries": sorted(regs),
             "smem_arrays": [],
             "i_ext": [int(min(e[0][0] for e in all_exts)), int(max(e[0][1] for e in all_exts))],
             "j_ext": [int(min(e[1][0] for e in all_exts)), int(max(e[1][1] for e in all_exts))]}

@@ -162,6 +162,8 @@ static void emu_lane_{name}() {{ {name}(*emu_args_{name}); }}
 extern "C" void emu_{name}(const Args *a, unsigned gx, unsigned gy, unsigned gz, unsigned bx, unsigned by, unsigned bz)
 {{
     emu_args_{name} = a;
+    static unsigned char *window = (unsigned char *)aligned_alloc(128, 256 * 1024);
+    emu_smem = window;
     blockDim = emu_dim3{{bx, by, bz}};
     gridDim = emu_dim3{{gx, gy, gz}};
     for (unsigned Z = 0; Z < gz; ++Z) for (unsigned Y = 0; Y < gy; ++Y) for (unsigned X = 0; X < gx; ++X) {{
@@ -323,7 +325,7 @@ def run(plan_dir: str, fields: dict, params: dict, origins: dict, domain, window
         getattr(a, t["name"] + "_s")[:] = strides
     for s in plan["scalars"]:
         setattr(a, s["name"], params[s["name"]])
-    if any(k["kind"] == "colfuse" for k in plan["kernels"]):  # bounds of every array, for the prefetch check
+    if any(k["kind"] in ("colfuse", "march") for k in plan["kernels"]):  # bounds of every array, for the prefetch check
         lib.emu_clear_ranges()
         lib.emu_add_range.argtypes = [ctypes.c_void_p, ctypes.c_size_t]
         for arr in list(fields.values()) + keep:

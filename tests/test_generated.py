@@ -374,9 +374,9 @@ _CASES += [("vertical_advection_dycore", (9, 5, 80)), ("vertical_advection_dycor
 @pytest.mark.parametrize("name,domain,knobs", [
     ("fv3_chain", (130, 37, 2), {"B200_MARCH_STRIP": "8"}),                              # 5 warps x 5 strips
     ("fv3_chain", (130, 21, 3), {"B200_MARCH_STRIP": "5", "B200_MARCH_COLUMNS": "2"}),   # two columns per lane
-    ("fv3_chain", (61, 19, 2), {"B200_MARCH_STRIP": "16", "B200_MARCH_PREFETCH": "0", "B200_MARCH_WARPS": "1"}),
+    ("fv3_chain", (61, 19, 2), {"B200_MARCH_STRIP": "16", "B200_MARCH_LEAD": "1", "B200_MARCH_WARPS": "1"}),
     ("horizontal_diffusion__tile", (120, 40, 2), {"B200_MARCH_STRIP": "8", "B200_MARCH_COLUMNS": "2"}),
-    ("exec_info_diffusion", (59, 33, 3), {"B200_MARCH_STRIP": "4", "B200_MARCH_PREFETCH": "3"}),
+    ("exec_info_diffusion", (59, 33, 3), {"B200_MARCH_STRIP": "4", "B200_MARCH_LEAD": "7"}),
     ("simple_horizontal_diffusion__tile", (63, 30, 2), {"B200_MARCH_STRIP": "8"}),
     ("native_functions__tile", (40, 13, 2), {"B200_MARCH_STRIP": "8", "B200_MARCH": "force"}),      # two stages: forced
     ("exec_info_advection__tile", (70, 23, 2), {"B200_MARCH_STRIP": "8", "B200_MARCH": "force", "B200_MARCH_COLUMNS": "2"}),

@@ -3,7 +3,7 @@
 GPU box (build container only; the directory is git-ignored but ships with gpurun).  The cubins are compiled here too
 (content-addressed cache under gt4py_b200/lib/cubin_cache), so the box only times.
 
-    python tools/make_march_variants.py [C:STRIP:PREFETCH:WARPS[:MIN_BLOCKS] ...]      tags: march_c<C>_s<STRIP>_p<P>_w<W>, smem
+    python tools/make_march_variants.py [C:STRIP:LEAD:WARPS[:MIN_BLOCKS] ...]      tags: march_c<C>_s<STRIP>_p<P>_w<W>, smem
 """
 import os
 import subprocess
@@ -45,7 +45,7 @@ def main():
         c, strip, pre, warps, *rest = spec.split(":")
         minb = rest[0] if rest else "0"
         jobs.append((f"march_c{c}_s{strip}_p{pre}_w{warps}" + (f"_b{minb}" if minb != "0" else ""),
-                     {"B200_MARCH_COLUMNS": c, "B200_MARCH_STRIP": strip, "B200_MARCH_PREFETCH": pre,
+                     {"B200_MARCH_COLUMNS": c, "B200_MARCH_STRIP": strip, "B200_MARCH_LEAD": pre,
                       "B200_MARCH_WARPS": warps, "B200_MARCH_MIN_BLOCKS": minb}, ""))
     procs = []
     for tag, env, opts in jobs:
