@@ -806,7 +806,7 @@ def run_configs(gb, _lib, storage, stencils, stream, roof, args):
             np.array_equal(tf["out"][:, js, :].asnumpy(), hostf["out"]))
         del tf, sets, h0, v0
 
-        # configs[3]: the FV3-style chain at 512x512x128, one generated fused tile kernel
+        # configs[3]: the FV3-style chain at 512x512x128, one generated fused kernel (warp-march form)
         cdom, hgt = (512, 512, 128), chain_oracle.HALO
         cn = cdom[0] * cdom[1] * cdom[2]
         st = generated.load_plan(os.path.join(ROOT, "tests", "golden", "generated", "fv3_chain"))
