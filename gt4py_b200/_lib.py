@@ -118,6 +118,7 @@ _PROTOTYPES = {
     "b200_stream_create": ([POINTER(_VP)], c_int),
     "b200_stream_destroy": ([_VP], c_int),
     "b200_stream_sync": ([_VP], c_int),
+    "b200_stream_l2_window": ([_VP, _VP, ctypes.c_size_t, ctypes.c_double, ctypes.POINTER(ctypes.c_size_t)], c_int),
     "b200_event_create": ([POINTER(_VP)], c_int),
     "b200_event_destroy": ([_VP], c_int),
     "b200_event_record": ([_VP, _VP], c_int),
@@ -225,6 +226,13 @@ class Stream:
 
     def synchronize(self):
         check(lib().b200_stream_sync(self.handle))
+
+    def l2_window(self, ptr: int = 0, nbytes: int = 0, hit_ratio: float = 1.0) -> int:
+        """Make accesses of this stream's work to [ptr, ptr + nbytes) persisting in L2 (b200_stream_l2_window; a field
+        one stencil writes and the next one reads); no arguments: remove the window.  Returns the bytes set aside."""
+        granted = ctypes.c_size_t(0)
+        check(lib().b200_stream_l2_window(self.handle, _VP(ptr or None), int(nbytes), float(hit_ratio), byref(granted)))
+        return int(granted.value)
 
     def wait_event(self, event: "Event"):
         check(lib().b200_stream_wait_event(self.handle, event.handle))

@@ -142,6 +142,49 @@ int b200_stream_sync(void *stream)
     B200_CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream));
     return B200_OK;
 }
+// L2 residency for a field that one stencil writes and the next one reads: the stream's access
+// policy window makes accesses to [ptr, ptr + bytes) persisting in the set-aside part of L2, everything else streaming.
+int b200_stream_l2_window(void *stream, const void *ptr, size_t bytes, double hit_ratio, size_t *granted)
+{
+    int dev = 0;
+    B200_CUDA_CHECK(cudaGetDevice(&dev));
+    int max_persist = 0, max_window = 0;
+    B200_CUDA_CHECK(cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, dev));
+    B200_CUDA_CHECK(cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, dev));
+    cudaStreamAttrValue attr;
+    memset(&attr, 0, sizeof(attr));
+    if (!ptr || !bytes) {  // switch off: no window, persisting lines back to normal
+        attr.accessPolicyWindow.num_bytes = 0;
+        attr.accessPolicyWindow.hitProp = cudaAccessPropertyNormal;
+        attr.accessPolicyWindow.missProp = cudaAccessPropertyNormal;
+        B200_CUDA_CHECK(cudaStreamSetAttribute((cudaStream_t)stream, cudaStreamAttributeAccessPolicyWindow, &attr));
+        B200_CUDA_CHECK(cudaCtxResetPersistingL2Cache());
+        if (granted) *granted = 0;
+        return B200_OK;
+    }
+    if (max_persist <= 0 || max_window <= 0) {
+        b200::set_error("stream_l2_window: this device has no persisting L2");
+        return B200_EINVAL;
+    }
+    const size_t carve = bytes < (size_t)max_persist ? bytes : (size_t)max_persist;
+    static size_t carved[64] = {0};  // per device: the set-aside only grows (setting the limit is a heavy call)
+    if (dev < 64 && carve > carved[dev]) {
+        B200_CUDA_CHECK(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, carve));
+        carved[dev] = carve;
+    }
+    const size_t window = bytes < (size_t)max_window ? bytes : (size_t)max_window;
+    attr.accessPolicyWindow.base_ptr = const_cast<void *>(ptr);
+    attr.accessPolicyWindow.num_bytes = window;
+    // a window larger than the set-aside: only that fraction of its lines is made persisting, the rest streams
+    double ratio = hit_ratio > 0 ? hit_ratio : 1.0;
+    if ((double)window * ratio > (double)carve) ratio = (double)carve / (double)window;
+    attr.accessPolicyWindow.hitRatio = (float)ratio;
+    attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+    attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+    B200_CUDA_CHECK(cudaStreamSetAttribute((cudaStream_t)stream, cudaStreamAttributeAccessPolicyWindow, &attr));
+    if (granted) *granted = carve;
+    return B200_OK;
+}
 int b200_event_create(void **event)
 {
     cudaEvent_t e;

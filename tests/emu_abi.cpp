@@ -103,6 +103,7 @@ int b200_fill_synthetic(const b200_field *f, const b200_field *base, uint64_t se
 int b200_stream_create(void **stream) { *stream = malloc(8); return B200_OK; }
 int b200_stream_destroy(void *stream) { free(stream); return B200_OK; }
 int b200_stream_sync(void *) { return B200_OK; }
+int b200_stream_l2_window(void *, const void *, size_t bytes, double, size_t *granted) { if (granted) *granted = bytes; return B200_OK; }
 int b200_event_create(void **event) { *event = malloc(8); return B200_OK; }
 int b200_event_destroy(void *event) { free(event); return B200_OK; }
 int b200_event_record(void *, void *) { return B200_OK; }

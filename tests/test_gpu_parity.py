@@ -437,3 +437,43 @@ def test_graph_replay_matches_direct_calls():
         from oracle import chain
 
         assert np.array_equal(c_out.asnumpy(), chain.fv3_chain(phi2, cf["u"], cf["v"], 0.05, 0.03))
+
+
+# ---- L2 access-policy window of a stream (b200_stream_l2_window) --------------------------------------------------
+def test_l2_window_changes_caching_not_results():
+    """Two generated stencils in a row, the second reading what the first wrote, on K slabs with the stream's
+    persisting-L2 window on the slab of the intermediate field (tools/l2_residency.py is the measurement): the window
+    is a caching hint only -- results are bit-identical with and without it, directly and from a captured graph."""
+    from gt4py_b200 import _lib, generated
+    from gt4py_b200.stencil_object import use_stream
+
+    ni, nj, nk, h, slab = 96, 70, 12, 2, 4
+    st = generated.load_plan(os.path.join(GOLDEN, "generated", "horizontal_diffusion"), use_library=False)
+    f = gen.hdiff_inputs(ni, nj, nk, seed=31)
+    want_mid = np.zeros_like(f["out_field"])
+    oracle.hdiff(f["in_field"], want_mid, f["coeff"], origin=(h, h, 0), domain=(ni, nj, nk))
+    dev = {k: _dev(v, (h, h, 0)) for k, v in f.items()}
+    mid = {False: storage.zeros(f["in_field"].shape, aligned_index=(h, h, 0)),
+           True: storage.zeros(f["in_field"].shape, aligned_index=(h, h, 0))}
+    out = {False: storage.zeros(f["in_field"].shape, aligned_index=(h, h, 0)),
+           True: storage.zeros(f["in_field"].shape, aligned_index=(h, h, 0))}
+    stream = _lib.Stream()
+
+    def one_pass(window):
+        level = mid[window].strides[2]
+        for k0 in range(0, nk, slab):
+            if window:
+                granted = stream.l2_window(mid[window].ptr + k0 * level, slab * level)
+                assert granted == slab * level
+            st(dev["in_field"], mid[window], dev["coeff"], origin=(h, h, k0), domain=(ni, nj, slab))
+            st(mid[window], out[window], dev["coeff"], origin=(2 * h, 2 * h, k0), domain=(ni - 2 * h, nj - 2 * h, slab))
+
+    with use_stream(stream):
+        one_pass(False)
+        one_pass(True)
+    stream.synchronize()
+    assert stream.l2_window() == 0  # window off, persisting lines reset
+    assert np.array_equal(mid[True].asnumpy()[h:-h, h:-h], want_mid[h:-h, h:-h])
+    assert np.array_equal(mid[True].asnumpy(), mid[False].asnumpy())
+    assert np.array_equal(out[True].asnumpy(), out[False].asnumpy())
+    assert np.abs(out[True].asnumpy()[2 * h:-2 * h, 2 * h:-2 * h]).sum() > 0
