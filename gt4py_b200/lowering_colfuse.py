@@ -152,12 +152,12 @@ class Analysis:
         written_in = [set(str(a.name) for sec in la for k, a, _, _ in sec if k == "w") for la in acc]
         touched_in = [set(str(a.name) for sec in la for _, a, _, _ in sec) for la in acc]
         self.written = set().union(*written_in)
-        # ---- cached fields: float64 IJK fields written in the run, touched only at (0, 0, 0) and (0, 0, prev) ------
+        # ---- cached fields: float64 / float32 IJK fields written in the run, touched only at (0, 0, 0) and (0, 0, prev) ------
         cached: Dict[str, Dict[str, Any]] = {}
         for name in sorted(self.written):
             f = _field(fields, name)
-            if not all(f["dims"]) or f["data_dims"] or f["dtype"] != common.DataType.FLOAT64:
-                continue
+            if not all(f["dims"]) or f["data_dims"] or f["dtype"] not in (common.DataType.FLOAT64, common.DataType.FLOAT32):
+                continue  # (a float32 value crosses the value stack as the double it converts to exactly)
             good = True
             for n, (loop, secs, backward) in enumerate(run_loops):
                 prev = 1 if backward else -1
@@ -340,7 +340,7 @@ def emit(kname: str, stencil: oir.Stencil, run: List[int], units_by_loop, block_
     S.append(f"        const bool live = i < a.ni + ({ihi}) && j < a.nj + ({jhi});")
     S += G
     for name in sorted(an.cached):
-        S.append(f"        double cur_{name} = 0.0, prev_{name} = 0.0;")
+        S.append(f"        {ct_of(name)} cur_{name} = 0, prev_{name} = 0;")
 
     for n, (loop, secs, backward) in enumerate(run_loops):
         step = -1 if backward else 1
@@ -386,7 +386,8 @@ def emit(kname: str, stencil: oir.Stencil, run: List[int], units_by_loop, block_
             while todo:
                 a_name = todo.pop(0)
                 pa = pslot[a_name]
-                if todo and pslot[todo[0]] == pa + 1 and pa % 2 == 0 and NP % 2 == 0:
+                if (todo and pslot[todo[0]] == pa + 1 and pa % 2 == 0 and NP % 2 == 0
+                        and ct_of(a_name) == "double" and ct_of(todo[0]) == "double"):
                     out.append(fmt2.format(s=f"k * {NP} + {pa}", a=a_name, b=todo.pop(0)))
                 else:
                     out.append(fmt1.format(s=f"k * {NP} + {pa}", a=a_name))
@@ -406,7 +407,7 @@ def emit(kname: str, stencil: oir.Stencil, run: List[int], units_by_loop, block_
                             "                cur_{a} = b200_stack_pop(cf_stk, {s});")
             for name in loads:
                 q = order.index((name, 0, 0))
-                S.append(f"                cur_{name} = rg{q}[(k & {table[(name, 0, 0)]['depth'] - 1}) * {T}];")
+                S.append(f"                cur_{name} = rg{q}[(k & {table[(name, 0, 0)]['depth'] - 1}) * {T * (8 // size_of[ct_of(name)])}];")
             for h in hs:
                 S.append(f"                if ({guards[id(h)]}) {{")
                 for d in L._declarations(h):
