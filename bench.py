@@ -724,9 +724,10 @@ def traffic_for(kernel, npts):
             table = json.load(fh)
     except Exception:
         return None
-    e = table.get(kernel)
-    if isinstance(e, dict) and e.get("points") == npts:
-        return e.get("bytes")
+    for key in (f"{kernel}@{npts}", kernel):  # one entry per (kernel, size)
+        e = table.get(key)
+        if isinstance(e, dict) and e.get("points") == npts:
+            return e.get("bytes")
     return None
 
 
