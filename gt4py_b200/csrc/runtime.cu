@@ -153,12 +153,19 @@ int b200_stream_l2_window(void *stream, const void *ptr, size_t bytes, double hi
     B200_CUDA_CHECK(cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, dev));
     cudaStreamAttrValue attr;
     memset(&attr, 0, sizeof(attr));
-    if (!ptr || !bytes) {  // switch off: no window, persisting lines back to normal
+    static size_t carved[64] = {0};  // per device: the set-aside only grows while windows are in use
+    if (!ptr || !bytes) {
+        // switch off: no window, persisting lines back to normal, and the set-aside returned -- it is taken from the L2
+        // every other kernel uses (measured: vadv at 2048x2048x80 2.72 -> 4.36 ms with 83 MB set aside)
         attr.accessPolicyWindow.num_bytes = 0;
         attr.accessPolicyWindow.hitProp = cudaAccessPropertyNormal;
         attr.accessPolicyWindow.missProp = cudaAccessPropertyNormal;
         B200_CUDA_CHECK(cudaStreamSetAttribute((cudaStream_t)stream, cudaStreamAttributeAccessPolicyWindow, &attr));
         B200_CUDA_CHECK(cudaCtxResetPersistingL2Cache());
+        if (dev < 64 && carved[dev]) {
+            B200_CUDA_CHECK(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, 0));
+            carved[dev] = 0;
+        }
         if (granted) *granted = 0;
         return B200_OK;
     }
@@ -167,8 +174,7 @@ int b200_stream_l2_window(void *stream, const void *ptr, size_t bytes, double hi
         return B200_EINVAL;
     }
     const size_t carve = bytes < (size_t)max_persist ? bytes : (size_t)max_persist;
-    static size_t carved[64] = {0};  // per device: the set-aside only grows (setting the limit is a heavy call)
-    if (dev < 64 && carve > carved[dev]) {
+    if (dev < 64 && carve > carved[dev]) {  // (setting the limit is a heavy call: only when it has to grow)
         B200_CUDA_CHECK(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, carve));
         carved[dev] = carve;
     }

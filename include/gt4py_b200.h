@@ -114,7 +114,8 @@ B200_API int b200_stream_sync(void *stream);
 /* L2 residency of an inter-stencil field (no counterpart in the reference: its GPU backends leave caching to the
  * hardware).  Accesses of work launched on `stream` to [ptr, ptr + bytes) become persisting in
  * the set-aside part of L2 (cudaLimitPersistingL2CacheSize, grown to min(bytes, device maximum); *granted reports it),
- * everything else streams.  ptr == NULL or bytes == 0 removes the window and resets the persisting lines.  `stream`
+ * everything else streams.  ptr == NULL or bytes == 0 removes the window, resets the persisting lines and returns the
+ * set-aside (it is taken from the L2 every other kernel uses: do switch it off after use).  `stream`
  * must be a stream of b200_stream_create (the legacy NULL stream has no attributes).  hit_ratio <= 0 means 1. */
 B200_API int b200_stream_l2_window(void *stream, const void *ptr, size_t bytes, double hit_ratio, size_t *granted);
 B200_API int b200_event_create(void **event);
