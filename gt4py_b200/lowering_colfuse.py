@@ -27,6 +27,14 @@ from gt4py.cartesian.gtc import common, oir
 # threads of a CTA along I x J (one column each) and the levels the prefetch runs ahead; tuning hooks for A/B builds
 BX, BY = (int(x) for x in os.environ.get("B200_COLFUSE_BLOCK", "128x2").split("x"))
 LEAD = int(os.environ.get("B200_COLFUSE_LEAD", "6"))
+# two-loop runs (FORWARD then BACKWARD over all levels, or the reverse): the second loop of the previous tile runs
+# interleaved, level by level, with the first loop of the next tile -- two independent dependency chains per thread,
+# the schedule of the hand-written vadv.  OFF by default, by measurement (profiles/r2_colfuse_pipelined.jsonl, B200,
+# 1024x1024x80): vadv 0.898 ms sequential / 0.996 pipelined / 0.912 pipelined with the unguarded middle part, Thomas
+# solver 0.903 / 1.000 / 0.928 -- the generated kernels are bound by instruction issue (every thread issues its own
+# cp.async copies), not by the latency the second chain would hide; kept for parts where that differs, with a test.
+PIPELINE = os.environ.get("B200_COLFUSE_PIPELINE", "0") != "0"
+MIDPATH = os.environ.get("B200_COLFUSE_MIDPATH", "1") != "0"
 assert (BX * BY) % 128 == 0 and BX * BY <= 1024, "a fused column CTA is a whole number of 4-warp groups"
 
 
@@ -251,6 +259,8 @@ def emit(kname: str, stencil: oir.Stencil, run: List[int], units_by_loop, block_
         _, loop, units = units_by_loop[n]
         run_loops.append((loop, _sections(units[0][0]), loop.loop_order == common.LoopOrder.BACKWARD))
     an = Analysis(stencil, run_loops, fields, accessed_outside)
+    if PIPELINE and _pipelinable(run_loops):
+        return _emit_pipelined(kname, run, run_loops, an, block_ext, fields, scalar_names, L)
     all_h = [h for _, secs, _ in run_loops for _, hs in secs for h in hs]
     exts = [block_ext[id(h)] for h in all_h]
     ilo, ihi = min(e[0][0] for e in exts), max(e[0][1] for e in exts)
@@ -437,5 +447,353 @@ def emit(kname: str, stencil: oir.Stencil, run: List[int], units_by_loop, block_
     meta = {"name": kname, "kind": "colfuse", "block": [BX, BY], "i_ext": [int(ilo), int(ihi)], "j_ext": [int(jlo), int(jhi)],
             "ring_slots": int(ring_slots), "stack_values_per_level": NP, "stack_tmem": NT, "loops": [int(x) for x in run],
             "cached": sorted(an.cached), "pushed": list(an.pushed),
+            "private": sorted(nm for nm, c in an.cached.items() if not c["store"])}
+    return "\n".join(src), meta
+
+
+def _full_range(secs, backward: bool) -> bool:
+    """Do the sections of a loop tile [START, END) exactly, in loop order?"""
+    first, last = secs[0][0], secs[-1][0]
+    lo, hi = (last.start, first.end) if backward else (first.start, last.end)
+    return (lo.level == common.LevelMarker.START and int(lo.offset) == 0
+            and hi.level == common.LevelMarker.END and int(hi.offset) == 0 and _contiguous(secs, backward))
+
+
+def _section_weight(interval) -> int:
+    """Levels of a section for a deep column (to pick a loop's longest section)."""
+    nk = 1000
+
+    def at(b):
+        return (nk if b.level == common.LevelMarker.END else 0) + int(b.offset)
+
+    return at(interval.end) - at(interval.start)
+
+
+def _pipelinable(run_loops) -> bool:
+    if len(run_loops) != 2:
+        return False
+    (_, secs_a, back_a), (_, secs_b, back_b) = run_loops
+    return back_a != back_b and _full_range(secs_a, back_a) and _full_range(secs_b, back_b)
+
+
+def _emit_pipelined(kname, run, run_loops, an, block_ext, fields, scalar_names, L):
+    """The fused kernel of a two-loop run with the machine schedule of the hand-written vadv (csrc/vadv_fused.cu): per
+    CTA, round r runs loop B (the second loop) of tile r - 1 and loop A (the first loop) of tile r level by level in ONE
+    loop -- two independent dependency chains per thread, which is what hides the latency of the division chain with
+    8 resident warps.  The value stack changes direction from tile to tile: the slot loop B pops at an iteration is
+    the slot loop A refills in the same iteration (slot of level k: k for even tiles, nk - 1 - k for odd ones).  Each
+    loop has its own prefetch ring and its own register set (nothing crosses from A to B except through the stack)."""
+    all_h = [h for _, secs, _ in run_loops for _, hs in secs for h in hs]
+    exts = [block_ext[id(h)] for h in all_h]
+    ilo, ihi = min(e[0][0] for e in exts), max(e[0][1] for e in exts)
+    jlo, jhi = min(e[1][0] for e in exts), max(e[1][1] for e in exts)
+    locals_ = {d.name for h in all_h for d in h.declarations}
+    gen = L.ExprGen(fields, scalar_names, locals_, True)
+    never_written = {str(f) for f in fields} - an.written
+    read_anywhere = set().union(*an.touched_in)
+    gen.readonly = {n for n in never_written if n in read_anywhere}
+    gen.cf_cached = an.cached
+    NP = len(an.pushed)
+    pslot = {name: p for p, name in enumerate(an.pushed)}
+    T, NT = BX * BY, tmem_values(BX * BY)
+    size_of = {"double": 8, "float": 4, "int64_t": 8, "int32_t": 4}
+
+    def ct_of(name):
+        return L.CTYPES[_field(fields, name)["dtype"]]
+
+    # ring layout: both loops are live at once, so their rings lie side by side
+    ring_of_loop, off = [], 0
+    for keys in an.ring:
+        table = {}
+        for key in sorted(keys):
+            dks = keys[key]["dk"]
+            depth = pow2ceil(LEAD + (max(dks) - min(dks)) + 1)
+            table[key] = {"slot": off, "depth": depth, "dkmin": min(dks), "dkmax": max(dks), **keys[key]}
+            off += depth
+        ring_of_loop.append(table)
+    ring_slots = off
+
+    def guard_text(h):
+        e = block_ext[id(h)]
+        return f"i >= {e[0][0]} && i < a.ni + ({e[0][1]}) && j >= {e[1][0]} && j < a.nj + ({e[1][1]})"
+
+    def index_at(name, di, dj, level):
+        f = _field(fields, name)
+        terms = []
+        if f["dims"][0]:
+            terms.append(f"(idx_t)(i + ({di})) * S0(a.{name}_s[0])")
+        if f["dims"][1]:
+            terms.append(f"(idx_t)(j + ({dj})) * (idx_t)a.{name}_s[1]")
+        if f["dims"][2]:
+            terms.append(f"(idx_t)({level}) * (idx_t)a.{name}_s[2]")
+        return " + ".join(terms) if terms else "0"
+
+    def fold(fn, items):
+        items = sorted(set(items))
+        text = items[0]
+        for x in items[1:]:
+            text = f"{fn}({text}, {x})"
+        return text
+
+    S = []
+    S.append("    typedef typename b200_idx<U>::type idx_t;")
+    for name in (str(f) for f in fields if str(f) in gen.readonly):
+        S.append(f"    const {ct_of(name)} *__restrict__ g_{name} = a.{name};")
+    S.append("    extern __shared__ __align__(16) unsigned char b200_smem[];")
+    S.append("    __shared__ unsigned cf_tmem_slot;")
+    S.append("    const int tid = (int)(threadIdx.y * blockDim.x + threadIdx.x);")
+    S.append("    double *const cf_ring = reinterpret_cast<double *>(b200_smem) + tid;")
+    S.append("    b200_stack cf_stk;")
+    S.append(f"    cf_stk.n_tmem = {NT};")
+    S.append(f"    cf_stk.cta = {T};")
+    S.append(f"    cf_stk.tmem = b200_stack_setup(&cf_tmem_slot, {NT});")
+    S.append(f"    cf_stk.smem = reinterpret_cast<double *>(b200_smem) + {ring_slots} * {T} + tid;")
+    S.append(f"    cf_stk.n_smem = a.cf_{kname}_smem;")
+    S.append(f"    cf_stk.nthreads = (long long)gridDim.x * {T};")
+    S.append(f"    cf_stk.spill = a.cf_{kname}_spill + (long long)blockIdx.x * {T} + tid;")
+    S.append(f"    const int cf_tiles_i = (a.ni + ({ihi - ilo}) + {BX - 1}) / {BX};")
+    S.append(f"    const int cf_tiles = cf_tiles_i * ((a.nj + ({jhi - jlo}) + {BY - 1}) / {BY});")
+    S.append("    const int cf_mine = (int)blockIdx.x < cf_tiles ? (cf_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;")
+    S.append("    const int nk = a.nk;")
+    # per-loop contexts: tile coordinates, guards, register sets
+    guard_names: List[Dict[int, str]] = []
+    for n, (loop, secs, backward) in enumerate(run_loops):
+        X = "AB"[n]
+        S.append(f"    int i{X} = 0, j{X} = 0;  // the tile loop {X} works on")
+        by_text: Dict[str, str] = {}
+        names: Dict[int, str] = {}
+        for _, hs in secs:
+            for h in hs:
+                text = guard_text(h)
+                if text not in by_text:
+                    by_text[text] = f"g{X}{len(by_text)}"
+                    S.append(f"    bool {by_text[text]} = false;")
+                names[id(h)] = by_text[text]
+        guard_names.append(names)
+        for name in sorted(an.cached):
+            if name in an.touched_in[n]:
+                S.append(f"    {ct_of(name)} cur{X}_{name} = 0, prev{X}_{name} = 0;")
+
+    set_tile = []  # text that (re)computes a loop's tile context from a tile number
+    for n, (loop, secs, backward) in enumerate(run_loops):
+        X = "AB"[n]
+        lines = [f"i{X} = ({ilo}) + (tile % cf_tiles_i) * {BX} + (int)threadIdx.x; "
+                 f"j{X} = ({jlo}) + (tile / cf_tiles_i) * {BY} + (int)threadIdx.y;",
+                 f"{{ const int i = i{X}, j = j{X}; const bool live = i < a.ni + ({ihi}) && j < a.nj + ({jhi});"]
+        seen = set()
+        for _, hs in secs:
+            for h in hs:
+                g = guard_names[n][id(h)]
+                if g not in seen:
+                    seen.add(g)
+                    lines.append(f"  {g} = live && {guard_text(h)};")
+        lines.append("}")
+        for name in sorted(an.cached):
+            if name in an.touched_in[n]:
+                lines.append(f"cur{X}_{name} = 0; prev{X}_{name} = 0;")
+        set_tile.append(lines)
+
+    level_fn, issue_fn, prologue = [], [], []
+    mid_range: List[Tuple[str, str]] = []
+    inside: List[str] = []
+    for n, (loop, secs, backward) in enumerate(run_loops):
+        X = "AB"[n]
+        step = -1 if backward else 1
+        table = ring_of_loop[n]
+        gen.cf_prev = 1 if backward else -1
+        gen.cf_ring = {}
+        order = sorted(table)
+        issue = []
+        span = max([t["dkmax"] - t["dkmin"] for t in table.values()], default=0)
+        for q, key in enumerate(order):
+            t = table[key]
+            name, di, dj = key
+            ct = ct_of(name)
+            per = 8 // size_of[ct]
+            S.append(f"    {ct} *const rg{X}{q} = reinterpret_cast<{ct} *>(cf_ring + {t['slot']} * {T});  // loop {X}: {name}[{di},{dj}]")
+            gen.cf_ring[key] = (f"rg{X}{q}", t["depth"] - 1, T * per)
+            far = t["dkmax"] if step > 0 else t["dkmin"]
+            use_guards = sorted({guard_names[n][id(h)] for _, h in t["uses"]})
+            lows, highs = [], []
+            for s_idx, dks in sorted(t["dk_by_sec"].items()):
+                lo, hi = L._interval_cond(secs[s_idx][0])
+                lows.append(f"({lo}) + ({min(dks)})")
+                highs.append(f"({hi}) + ({max(dks)})")
+            S.append(f"    const int lo{X}{q} = {fold('min', lows)}, hi{X}{q} = {fold('max', highs)};")
+            fn = "b200_cp_async8" if size_of[ct] == 8 else "b200_cp_async4"
+            issue.append(f"{{ const int lv = kv + ({step * LEAD + far}); const bool ok = ({' || '.join(use_guards)}) && "
+                         f"lv >= lo{X}{q} && lv < hi{X}{q}; {fn}(rg{X}{q} + (lv & {t['depth'] - 1}) * {T * per}, "
+                         f"a.{name} + (ok ? {index_at(name, di, dj, 'lv')} : 0), ok); }}")
+        # the copies of one more level of loop X's inputs (no commit: the caller commits once per iteration)
+        F = [f"    auto cf_issue{X} = [&](const int kv) {{", f"        const int i = i{X}, j = j{X}; (void)i; (void)j;"]
+        F += ["        " + x for x in issue] + ["    };"]
+        issue_fn.append((F, bool(issue)))
+        first = "nk - 1" if backward else "0"
+        prologue.append(f"for (int t = {LEAD + span}; t >= 1; --t) {{ cf_issue{X}({first} - ({step}) * t); b200_cp_commit(); }}"
+                        if issue else "")
+        pops, loads, pushes = sorted(an.pop[n]), sorted(an.load[n]), sorted(an.push[n])
+
+        def paired(todo, fmt2, fmt1):
+            out, todo = [], list(todo)
+            while todo:
+                a_name = todo.pop(0)
+                pa = pslot[a_name]
+                if (todo and pslot[todo[0]] == pa + 1 and pa % 2 == 0 and NP % 2 == 0
+                        and ct_of(a_name) == "double" and ct_of(todo[0]) == "double"):
+                    out.append(fmt2.format(s=f"sl * {NP} + {pa}", a=a_name, b=todo.pop(0)))
+                else:
+                    out.append(fmt1.format(s=f"sl * {NP} + {pa}", a=a_name))
+            return out
+
+        # one level of loop X: k = the level, sl = its stack slot (the direction alternates from tile to tile)
+        F = [f"    auto cf_level{X} = [&](const int k, const int sl) {{",
+             f"        const int i = i{X}, j = j{X}; (void)i; (void)j; (void)sl;"]
+        for name in sorted(an.cached):
+            if name in an.touched_in[n]:
+                F.append(f"        {ct_of(name)} &cur_{name} = cur{X}_{name}, &prev_{name} = prev{X}_{name}; (void)prev_{name};")
+        for g in sorted(set(guard_names[n].values())):
+            F.append(f"        const bool {g[:1] + g[2:]} = {g};")  # gA0 -> g0 (the name the bodies were written with)
+        if pops:
+            F.append("        __syncwarp();")
+            F += paired(pops, "        b200_stack_pop2(cf_stk, {s}, cur_{a}, cur_{b});",
+                        "        cur_{a} = b200_stack_pop(cf_stk, {s});")
+        for name in loads:
+            q = order.index((name, 0, 0))
+            F.append(f"        cur_{name} = rg{X}{q}[(k & {table[(name, 0, 0)]['depth'] - 1}) * {T * (8 // size_of[ct_of(name)])}];")
+        for s_idx, (interval, hs) in enumerate(secs):
+            lo, hi = L._interval_cond(interval)
+            F.append(f"        {'if' if s_idx == 0 else 'else if'} (k >= ({lo}) && k < ({hi})) {{")
+            for h in hs:
+                g = guard_names[n][id(h)]
+                F.append(f"            if ({g[:1] + g[2:]}) {{")
+                for d in L._declarations(h):
+                    F.append(" " * 16 + f"{L.CTYPES[d.dtype]} {d.name} = 0;")
+                F += gen.stmts(h.body, 16)
+                F.append("            }")
+            F.append("        }")
+        if pushes:
+            F.append("        __syncwarp();")
+            F += paired(pushes, "        b200_stack_push2(cf_stk, {s}, cur_{a}, cur_{b});",
+                        "        b200_stack_push(cf_stk, {s}, cur_{a});")
+        for name in sorted(an.reads_prev[n]):
+            F.append(f"        prev_{name} = cur_{name};")
+        F.append("    };")
+        level_fn.append(F)
+        # the loop's longest section once more, without section dispatch and without guards: for iterations where the
+        # tile is entirely inside the domain -- straight-line code that the compiler can interleave with the other loop's
+        mid = max(range(len(secs)), key=lambda q: _section_weight(secs[q][0]))
+        interval, hs = secs[mid]
+        lo, hi = L._interval_cond(interval)
+        mid_range.append((f"nk - ({hi})", f"nk - ({lo})") if backward else (lo, hi))  # in iteration space
+        M = [f"    auto cf_mid{X} = [&](const int k, const int sl) {{",
+             f"        const int i = i{X}, j = j{X}; (void)i; (void)j; (void)sl;"]
+        for name in sorted(an.cached):
+            if name in an.touched_in[n]:
+                M.append(f"        {ct_of(name)} &cur_{name} = cur{X}_{name}, &prev_{name} = prev{X}_{name}; (void)prev_{name};")
+        if pops:
+            M.append("        __syncwarp();")
+            M += paired(pops, "        b200_stack_pop2(cf_stk, {s}, cur_{a}, cur_{b});",
+                        "        cur_{a} = b200_stack_pop(cf_stk, {s});")
+        for name in loads:
+            q = order.index((name, 0, 0))
+            M.append(f"        cur_{name} = rg{X}{q}[(k & {table[(name, 0, 0)]['depth'] - 1}) * {T * (8 // size_of[ct_of(name)])}];")
+        for h in hs:
+            M.append("        {")
+            for d in L._declarations(h):
+                M.append(" " * 12 + f"{L.CTYPES[d.dtype]} {d.name} = 0;")
+            M += gen.stmts(h.body, 12)
+            M.append("        }")
+        if pushes:
+            M.append("        __syncwarp();")
+            M += paired(pushes, "        b200_stack_push2(cf_stk, {s}, cur_{a}, cur_{b});",
+                        "        b200_stack_push(cf_stk, {s}, cur_{a});")
+        for name in sorted(an.reads_prev[n]):
+            M.append(f"        prev_{name} = cur_{name};")
+        M.append("    };")
+        level_fn.append(M)
+        # "every guard of the loop holds for every thread of the CTA": the tile lies inside the domain
+        es = [block_ext[id(h)] for _, hs_ in secs for h in hs_]
+        inside.append(f"(i{X} - (int)threadIdx.x) >= ({max(e[0][0] for e in es)}) && "
+                      f"(i{X} - (int)threadIdx.x) + {BX} <= a.ni + ({min(e[0][1] for e in es)}) && "
+                      f"(j{X} - (int)threadIdx.y) >= ({max(e[1][0] for e in es)}) && "
+                      f"(j{X} - (int)threadIdx.y) + {BY} <= a.nj + ({min(e[1][1] for e in es)})")
+    for F, _ in issue_fn:
+        S += F
+    for F in level_fn:
+        S += F
+    backA, backB = run_loops[0][2], run_loops[1][2]
+    kA = "nk - 1 - it" if backA else "it"
+    kB = "nk - 1 - it" if backB else "it"
+    has_issue = [x[1] for x in issue_fn]
+
+    def round_loop(doA: bool, doB: bool) -> List[str]:
+        if doA and doB and MIDPATH:
+            # iterations in which both loops are in their longest section, in a CTA whose two tiles lie inside the
+            # domain: the unguarded bodies; the iterations before and after them (and every other CTA): the general form
+            R = [f"            const bool fast = ({inside[0]}) && ({inside[1]});  // CTA-uniform: both tiles inside the domain",
+                 f"            const int m0 = fast ? max(max({mid_range[0][0]}, {mid_range[1][0]}), 0) : nk;",
+                 f"            const int m1 = fast ? max(min(min({mid_range[0][1]}, {mid_range[1][1]}), nk), m0) : nk;"]
+            for lo_, hi_, fastpart in (("0", "m0", False), ("m0", "m1", True), ("m1", "nk", False)):
+                R += [f"            for (int it = {lo_}; it < {hi_}; ++it) {{",
+                      f"                const int kA = {kA}, kB = {kB};"]
+                if has_issue[0]:
+                    R.append("                cf_issueA(kA);")
+                if has_issue[1]:
+                    R.append("                cf_issueB(kB);")
+                if has_issue[0] or has_issue[1]:
+                    R.append(f"                b200_cp_commit(); b200_cp_wait<{LEAD}>();")
+                fnB, fnA = ("cf_midB", "cf_midA") if fastpart else ("cf_levelB", "cf_levelA")
+                R.append(f"                {fnB}(kB, parB ? nk - 1 - kB : kB);")
+                R.append(f"                {fnA}(kA, parA ? nk - 1 - kA : kA);")
+                R.append("            }")
+            return R
+        R = ["            for (int it = 0; it < nk; ++it) {", f"                const int kA = {kA}, kB = {kB}; (void)kA; (void)kB;"]
+        if doA and has_issue[0]:
+            R.append("                cf_issueA(kA);")
+        if doB and has_issue[1]:
+            R.append("                cf_issueB(kB);")
+        if (doA and has_issue[0]) or (doB and has_issue[1]):
+            R.append(f"                b200_cp_commit(); b200_cp_wait<{LEAD}>();")
+        # the stack slot of a level: the level itself for even tiles of loop A's direction, mirrored for odd ones
+        if doB:
+            R.append("                cf_levelB(kB, parB ? nk - 1 - kB : kB);")
+        if doA:
+            R.append("                cf_levelA(kA, parA ? nk - 1 - kA : kA);")
+        R.append("            }")
+        return R
+
+    S.append("    for (int r = 0; r <= cf_mine && cf_mine > 0; ++r) {")
+    S.append("        const bool doA = r < cf_mine, doB = r > 0;")
+    S.append("        const int parA = r & 1, parB = parA ^ 1; (void)parA; (void)parB;")
+    S.append("        if (doA) { const int tile = (int)blockIdx.x + r * (int)gridDim.x;")
+    S += ["            " + x for x in set_tile[0]]
+    if prologue[0]:
+        S.append("            " + prologue[0])
+    S.append("        }")
+    if prologue[1]:
+        S.append("        if (doB) { " + prologue[1] + " }")
+    S.append("        if (doA && doB) {")
+    S += round_loop(True, True)
+    S.append("        } else if (doA) {")
+    S += round_loop(True, False)
+    S.append("        } else {")
+    S += round_loop(False, True)
+    S.append("        }")
+    S.append("        b200_cp_wait<0>();")
+    S.append("        b200_stack_fence();")
+    S.append("        if (doA) {  // the tile loop A just finished is loop B's next one")
+    S.append("            const int tile = (int)blockIdx.x + r * (int)gridDim.x;")
+    S += ["            " + x for x in set_tile[1]]
+    S.append("        }")
+    S.append("    }")
+    S.append("    b200_stack_teardown(&cf_tmem_slot);")
+    gen.cf_ring, gen.cf_cached = {}, {}
+    src = [f"template <bool U> __device__ __forceinline__ void {kname}_impl(const Args &a)", "{"] + S + ["}"]
+    for suffix, flag in (("", "false"), ("_u", "true")):
+        src.append(f'extern "C" __global__ void __launch_bounds__({BX * BY}, 1) {kname}{suffix}(const Args a) '
+                   f"{{ {kname}_impl<{flag}>(a); }}")
+    meta = {"name": kname, "kind": "colfuse", "block": [BX, BY], "i_ext": [int(ilo), int(ihi)], "j_ext": [int(jlo), int(jhi)],
+            "ring_slots": int(ring_slots), "stack_values_per_level": NP, "stack_tmem": NT, "loops": [int(x) for x in run],
+            "cached": sorted(an.cached), "pushed": list(an.pushed), "pipelined": True,
             "private": sorted(nm for nm, c in an.cached.items() if not c["store"])}
     return "\n".join(src), meta

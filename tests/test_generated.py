@@ -391,6 +391,19 @@ def test_warp_march_kernels_over_strips_and_knobs(name, domain, knobs, monkeypat
     test_lowering_against_the_reference_at_other_sizes(name, domain, rebuild=True, expect_kind="march")
 
 
+@pytest.mark.parametrize("name,domain", [("vertical_advection_dycore", (300, 7, 66)), ("tridiagonal_solver", (260, 5, 70)),
+                                         ("column_physics", (131, 6, 9)), ("vertical_advection_dycore__f32", (40, 3, 90))])
+def test_pipelined_column_kernels(name, domain, monkeypatch):
+    """The pipelined schedule of the fused column template (lowering_colfuse.PIPELINE, off by default): loop B of the
+    previous tile interleaved with loop A of the next one, stack direction alternating from tile to tile, unguarded
+    middle part for tiles inside the domain.  More tiles than CTAs, ragged edges; bit-exact against the reference."""
+    _gt4py()
+    from gt4py_b200 import lowering_colfuse
+
+    monkeypatch.setattr(lowering_colfuse, "PIPELINE", True)
+    test_lowering_against_the_reference_at_other_sizes(name, domain, rebuild=True, expect_kind="colfuse")
+
+
 @pytest.mark.parametrize("name,domain", _CASES)
 def test_lowering_against_the_reference_at_other_sizes(name, domain, rebuild=False, expect_kind=None):
     """Differential test in the build container: the reference's numpy backend and the host-emulated kernels of a
