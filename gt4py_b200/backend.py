@@ -114,6 +114,7 @@ class B200Backend(BaseBackend):
         "k_register_cache": {"versioning": True, "type": bool},
         "fuse_columns": {"versioning": True, "type": bool},
         "warp_march": {"versioning": True, "type": bool},
+        "level_fission": {"versioning": True, "type": bool},
     }
     storage_info: ClassVar[layout.LayoutInfo] = {
         "alignment": storage.ALIGNMENT,
@@ -174,13 +175,14 @@ class B200Backend(BaseBackend):
         kc = bool(self.builder.options.backend_opts.get("k_register_cache", False))
         fc = bool(self.builder.options.backend_opts.get("fuse_columns", True))
         wm = bool(self.builder.options.backend_opts.get("warp_march", True))
+        lf = bool(self.builder.options.backend_opts.get("level_fission", True))
         if fuse is None or fuse:
-            plan, source = lowering.lower(self.oir(True), name, fuse=True, k_register_cache=kc, fuse_columns=fc, warp_march=wm)
+            plan, source = lowering.lower(self.oir(True), name, fuse=True, k_register_cache=kc, fuse_columns=fc, warp_march=wm, level_fission=lf)
             deepest = max([k.get("stages", 0) for k in plan["kernels"]], default=0)
             if fuse is None and deepest < self.AUTO_FUSE_MIN_STAGES:
                 fuse = False
         if fuse is not None and not fuse:
-            plan, source = lowering.lower(self.oir(False), name, fuse=False, k_register_cache=kc, fuse_columns=fc, warp_march=wm)
+            plan, source = lowering.lower(self.oir(False), name, fuse=False, k_register_cache=kc, fuse_columns=fc, warp_march=wm, level_fission=lf)
         match = self.library_match()
         if match is not None:
             plan["library"] = match

@@ -44,8 +44,10 @@ CASES = {
     "vertical_advection_dycore__kcache": ((257, 130, 65), None, "_u"),
     "horizontal_region_with_conditional": ((300, 211, 40), None, None),
     "runtime_if": ((310, 200, 40), None, None),
-    "seq_exchange": ((301, 130, 48), ["level", "level"], "_u"),      # per-level launches (FORWARD)
-    "seq_exchange_backward": ((259, 133, 37), ["level"] * 3, "_u"),  # ... BACKWARD, three stages
+    "seq_exchange": ((301, 130, 48), ["column", "column"], "_u"),           # loop fission (FORWARD)
+    "seq_exchange_backward": ((259, 133, 37), ["column"] * 3, "_u"),        # ... BACKWARD, three stages
+    "seq_exchange__level": ((301, 130, 48), ["level", "level"], "_u"),      # per-level launches (fission off)
+    "seq_exchange_backward__level": ((259, 133, 37), ["level"] * 3, "_u"),
 }
 
 

@@ -128,22 +128,25 @@ def body_chain():
 
 
 def body_sequential_exchange():
-    """FORWARD / BACKWARD loops whose stages exchange values horizontally inside a level (chain_definitions.py):
-    `level` kernels launched level by level by the C plan launcher; bit-exact with the reference's numpy backend."""
+    """FORWARD / BACKWARD loops whose stages exchange values horizontally inside a level (chain_definitions.py): by
+    default loop fission turns them into column kernels (the exchanged temporary does not depend on the carried values);
+    with `level_fission=False` they run as `level` kernels launched level by level by the C plan launcher.  Both
+    bit-exact with the reference's numpy backend."""
     gtscript, gt_storage, _ = _gt4py()
     from tests import chain_definitions as cd
 
     dom = (14, 9, 7) if EMU else (150, 67, 33)
     for n, definition in enumerate((cd.seq_exchange, cd.seq_exchange_backward)):
-        st_dev, st_ref = _both(gtscript, definition)
-        rng = np.random.default_rng(20 + n)
-        f = {k: rng.uniform(-1.0, 1.5, (dom[0] + 2, dom[1] + 2, dom[2])) for k in ("a", "b")}
-        f["out"] = np.zeros(f["a"].shape)
-        _run_pair(gt_storage, st_dev, st_ref, f, {}, (1, 1, 0), dom, ["out"], aligned={k: (1, 1, 0) for k in f})
-        impl = type(st_dev)._b200()
-        kinds = [k["kind"] for k in impl._plan_["kernels"]]
-        assert kinds == ["level"] * (2 + n)
-        assert impl._last_entry_points == [k["name"] + "_u" for k in impl._plan_["kernels"]]
+        for fission in (True, False):
+            st_dev, st_ref = _both(gtscript, definition, level_fission=fission)
+            rng = np.random.default_rng(20 + n)
+            f = {k: rng.uniform(-1.0, 1.5, (dom[0] + 2, dom[1] + 2, dom[2])) for k in ("a", "b")}
+            f["out"] = np.zeros(f["a"].shape)
+            _run_pair(gt_storage, st_dev, st_ref, f, {}, (1, 1, 0), dom, ["out"], aligned={k: (1, 1, 0) for k in f})
+            impl = type(st_dev)._b200()
+            kinds = [k["kind"] for k in impl._plan_["kernels"]]
+            assert kinds == (["column"] if fission else ["level"]) * (2 + n)
+            assert impl._last_entry_points == [k["name"] + "_u" for k in impl._plan_["kernels"]]
 
 
 def body_storage_drop_in():

@@ -83,6 +83,9 @@ def definitions():
     # ... and through the shared-memory tile kernel instead of the warp-march form (lowering_march.py)
     for name in ("fv3_chain", "exec_info_diffusion", "horizontal_diffusion", "exec_info_advection"):
         defs[name + "__smem"] = (*defs[name][:2], {"fuse_temporaries": True, "warp_march": False})
+    # sequential loops whose stages exchange values horizontally, run level by level (loop fission switched off)
+    for name in ("seq_exchange", "seq_exchange_backward"):
+        defs[name + "__level"] = (*defs[name][:2], {"level_fission": False})
     # column kernels with the K register cache (rolling buffer) switched on; library matching off so that the
     # lowered kernels are what runs
     for name in ("vertical_advection_dycore", "tridiagonal_solver", "column_physics", "while_stencil"):
