@@ -346,7 +346,11 @@ static int launch_fused2(const VadvArgs &a, cudaStream_t stream, bool *handled)
     const int tmem_slots = VM_TMEM_LEVELS / FK;  // stage slots of 4 * FK columns per thread
     const int nTs = nstages < tmem_slots ? nstages : tmem_slots;
     const size_t slot_bytes = (size_t)2 * FK * VM_COLS * 8;
-    const int want_s = env_s > 0 ? env_s : (FK == 2 ? 5 : 3);
+    // ring depths, measured on B200 (tools/vadv_knob_sweep.py, profiles/r2_vadv_ring_depth.jsonl): a forward ring of 7
+    // stages beats 5 by 2-3 % at 2048 x 2048 x 80 (2.72 -> 2.66 ms) and by 0.6 % at 1024 x 1024 x 80; the backward ring
+    // (u_pos only) gives up two of its 6 stages when that is what lets the seventh forward stage fit (nk = 80: the
+    // LIFO's shared-memory part takes 64 KB)
+    const int want_s = env_s > 0 ? env_s : (FK == 2 ? 7 : 3);
     const int want_sb = env_sb > 0 ? env_sb : (FK == 2 ? 6 : 3);
     // 1. whole LIFO on chip, rings shrunk if need be (down to 2 stages)
     size_t lifo = (size_t)(nstages - nTs) * slot_bytes;
@@ -354,6 +358,8 @@ static int launch_fused2(const VadvArgs &a, cudaStream_t stream, bool *handled)
     int SB = want_sb > VM_MAX_STAGES ? VM_MAX_STAGES : want_sb;
     long avail = (long)max_smem - VM_BAR_BYTES - (long)lifo;
     while (SB > 2 && (long)SB * G::SLOT_B > avail / 4) --SB;
+    if (env_sb <= 0 && FK == 2)  // the forward ring first: shrink the backward ring to 4 if that buys a forward stage
+        while (SB > 4 && (avail - (long)SB * G::SLOT_B) / (long)G::SLOT_F < want_s) --SB;
     avail -= (long)SB * G::SLOT_B;
     int S = avail > 0 ? (int)(avail / G::SLOT_F) : 0;
     if (S > want_s) S = want_s;
