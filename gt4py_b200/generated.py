@@ -16,6 +16,7 @@ import hashlib
 import json
 import os
 import subprocess
+import threading
 from ctypes import byref, c_void_p
 from typing import Any, Dict
 
@@ -45,7 +46,8 @@ def compile_cubin(src_path: str) -> str:
         digest = hashlib.sha256(fh.read() + " ".join(NVCC_FLAGS).encode()).hexdigest()[:24]
     out = os.path.join(cubin_cache_dir(), f"{digest}.cubin")
     if not os.path.exists(out):
-        tmp = f"{out}.{os.getpid()}.tmp"
+        # unique per process AND thread: two plans with identical kernels (same digest) may compile at the same time
+        tmp = f"{out}.{os.getpid()}.{threading.get_ident()}.tmp"
         cmd = [_build.nvcc(), *NVCC_FLAGS, "-cubin", "-o", tmp, src_path]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode:
