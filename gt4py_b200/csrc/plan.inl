@@ -227,7 +227,7 @@ static int parse(Plan &p, const std::string &text)
                 }
             }
             else if (kind == "tile") { k.kind = K_TILE; ls >> k.ti >> k.tj >> k.bx >> k.by >> k.smem >> k.has_tma >> k.smem_tma; }
-            else if (kind == "colfuse") { k.kind = K_COLFUSE; ls >> k.bx >> k.by >> k.ring_slots >> k.stack_values >> k.stack_tmem; }
+            else if (kind == "colfuse") { k.kind = K_COLFUSE; ls >> k.bx >> k.by >> k.ring_slots >> k.stack_values >> k.stack_tmem >> k.has_tma >> k.smem_tma; }
             else return fail(B200_EINVAL, "plan descriptor: unknown kernel kind '%s'", kind.c_str());
             if (!ls) return fail(B200_EINVAL, "plan descriptor: bad kernel line '%s'", line.c_str());
             p.kernels.push_back(k);
@@ -334,6 +334,7 @@ static int create(const char *desc, size_t desc_bytes, const void *image, size_t
         if (k.kind == K_COLFUSE) {
             rc = b200_kernel_set_smem(k.entry, B200_PLAN_COLFUSE_SMEM);
             if (!rc) rc = b200_kernel_set_smem(k.entry_u, B200_PLAN_COLFUSE_SMEM);
+            if (!rc && k.has_tma) rc = b200_kernel_set_smem(k.entry_t, B200_PLAN_COLFUSE_SMEM);
         } else if (k.kind == K_TILE || k.kind == K_MARCH) {
             if (k.smem > 48 * 1024) {
                 rc = b200_kernel_set_smem(k.entry, k.smem);
@@ -583,7 +584,8 @@ static int launch(Plan &p, const int64_t dom[3], const b200_field *fields, int n
             const int64_t slot = (int64_t)k.bx * k.by * 8;  // one value (or one ring level) of every thread of the CTA
             int64_t need = nk * k.stack_values - k.stack_tmem;
             if (need < 0) need = 0;
-            const int64_t ring = (int64_t)k.ring_slots * slot;
+            int64_t ring = (int64_t)k.ring_slots * slot;
+            if (tma_ok[n] == 1 && k.entry_t) { entry = k.entry_t; sfx = "_t"; ring = k.smem_tma; }  // rings fed by TMA
             int64_t n_smem = (B200_PLAN_COLFUSE_SMEM - ring) / slot;
             if (n_smem > need) n_smem = need;
             if (n_smem < 0) n_smem = 0;

@@ -84,8 +84,9 @@ def plan_descriptor(plan: Dict[str, Any]) -> str:
             L.append(f"{head} {k['tile'][0]} {k['tile'][1]} {k['block'][0]} {k['block'][1]} {k['smem_bytes']} "
                      f"{1 if tma else 0} {tma['smem_bytes'] if tma else 0}")
         elif k["kind"] == "colfuse":
+            tma = k.get("tma")
             L.append(f"{head} {k['block'][0]} {k['block'][1]} {k['ring_slots']} {k['stack_values_per_level']} "
-                     f"{k.get('stack_tmem', 128)}")
+                     f"{k.get('stack_tmem', 128)} {1 if tma else 0} {tma['smem_bytes'] if tma else 0}")
         else:
             L.append(head)
     for name, kind, ref, extra in plan["args"]:
@@ -161,8 +162,9 @@ class GeneratedStencil(StencilObject):
             cls._mod = _Module(cubin, names)
             for k in cls._plan_["kernels"]:
                 if k["kind"] == "colfuse":
-                    for sfx in ("", "_u"):
+                    for sfx in ("", "_u") + (("_t",) if "tma" in k else ()):
                         _lib.check(_lib.lib().b200_kernel_set_smem(cls._mod.kernels[k["name"] + sfx], _COLFUSE_SMEM))
+                    continue
                 for sfx, nbytes in (("", k.get("smem_bytes", 0)), ("_u", k.get("smem_bytes", 0)),
                                     ("_t", k.get("tma", {}).get("smem_bytes", 0))):
                     if nbytes > 48 * 1024:  # opt in to more than the default dynamic shared memory
@@ -421,6 +423,8 @@ class GeneratedStencil(StencilObject):
                 slot = bx * by * 8
                 need = max(0, nk * k["stack_values_per_level"] - k.get("stack_tmem", 128))
                 ring = k["ring_slots"] * slot
+                if tma_ok.get(k["name"]):  # the <k>_t entry: rings fed by TMA tile loads
+                    sfx, ring = "_t", k["tma"]["smem_bytes"]
                 n_smem = max(0, min(need, (_COLFUSE_SMEM - ring) // slot))
                 smem = ring + n_smem * slot
                 spill = self._cf_spill(k["name"], (need - n_smem) * ctas * bx * by * 8, stream)

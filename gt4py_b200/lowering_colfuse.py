@@ -35,6 +35,12 @@ LEAD = int(os.environ.get("B200_COLFUSE_LEAD", "6"))
 # cp.async copies), not by the latency the second chain would hide; kept for parts where that differs, with a test.
 PIPELINE = os.environ.get("B200_COLFUSE_PIPELINE", "0") != "0"
 MIDPATH = os.environ.get("B200_COLFUSE_MIDPATH", "1") != "0"
+# third entry point <k>_t: prefetch rings fed by TMA tile loads issued by one thread (see _emit_tma).  OFF by default, by
+# measurement (B200, 1024x1024x80, profiles/r2_colfuse_tma.jsonl): bit-exact, but vadv 2.04 ms against 0.90 ms with the
+# per-thread cp.async rings, Thomas solver 1.42 against 0.90, whatever the ring depth (8 or 16 slots) -- ncu: 30 % of all
+# stall samples sit in the loops that wait for a slot's `full` barrier, 587 M executed warp instructions against 200 M:
+# one level of boxes per slot issued from inside a consumer warp does not keep the rings ahead of 8 consumer warps.
+TMA_RINGS = os.environ.get("B200_COLFUSE_TMA", "0") != "0"
 assert (BX * BY) % 128 == 0 and BX * BY <= 1024, "a fused column CTA is a whole number of 4-warp groups"
 
 
@@ -448,7 +454,234 @@ def emit(kname: str, stencil: oir.Stencil, run: List[int], units_by_loop, block_
             "ring_slots": int(ring_slots), "stack_values_per_level": NP, "stack_tmem": NT, "loops": [int(x) for x in run],
             "cached": sorted(an.cached), "pushed": list(an.pushed),
             "private": sorted(nm for nm, c in an.cached.items() if not c["store"])}
+    if TMA_RINGS:
+        made = _emit_tma(kname, run_loops, an, block_ext, fields, scalar_names, L)
+        if made is not None:
+            src.append(made[0])
+            meta["tma"] = made[1]
     return "\n".join(src), meta
+
+
+def _emit_tma(kname, run_loops, an, block_ext, fields, scalar_names, L):
+    """Third entry point `<k>_t` of a fused column kernel: the prefetch rings are fed by TMA tile loads (one box per
+    field and level, issued by ONE thread of the CTA, completion on an mbarrier per ring slot) instead of one cp.async
+    per thread, field and level -- the copies are a quarter of the instructions of a level in the `_u` form.  Same
+    persistent-tile / value-stack structure.  Every thread waits on the slot's `full` barrier before it reads a level;
+    one lane per warp arrives on its `empty` barrier when the warp is done with it; the issuing thread (thread 0) runs
+    LEAD levels ahead inside the level loop, so no warp is set aside as a producer.  Levels and columns outside a field
+    are zero-filled by the hardware (never read: extent analysis).  Returns (source, tma meta) or None."""
+    size_of = {"double": 8, "float": 4, "int64_t": 8, "int32_t": 4}
+
+    def ct_of(name):
+        return L.CTYPES[_field(fields, name)["dtype"]]
+
+    if not any(an.ring):
+        return None
+    all_h = [h for _, secs, _ in run_loops for _, hs in secs for h in hs]
+    exts = [block_ext[id(h)] for h in all_h]
+    ilo, ihi = min(e[0][0] for e in exts), max(e[0][1] for e in exts)
+    jlo, jhi = min(e[1][0] for e in exts), max(e[1][1] for e in exts)
+    locals_ = {d.name for h in all_h for d in h.declarations}
+    gen = L.ExprGen(fields, scalar_names, locals_, True)
+    never_written = {str(f) for f in fields} - an.written
+    read_anywhere = set().union(*an.touched_in)
+    gen.readonly = {n for n in never_written if n in read_anywhere}
+    gen.cf_cached = an.cached
+    NP = len(an.pushed)
+    pslot = {name: p for p, name in enumerate(an.pushed)}
+    T, NT = BX * BY, tmem_values(BX * BY)
+    # one box per field, the same for every loop of the run (one tensor map per field): the hull of its offsets
+    hull: Dict[str, List[int]] = {}
+    for keys in an.ring:
+        for (name, di, dj) in keys:
+            if ct_of(name) not in size_of:
+                return None
+            h_ = hull.setdefault(name, [di, di, dj, dj])
+            h_[0], h_[1], h_[2], h_[3] = min(h_[0], di), max(h_[1], di), min(h_[2], dj), max(h_[3], dj)
+    box, foff, slot_bytes = {}, {}, 0
+    for name in sorted(hull):
+        item = size_of[ct_of(name)]
+        per16 = 16 // item
+        w = (BX + hull[name][1] - hull[name][0] + (per16 - 1) + per16 - 1) // per16 * per16
+        hgt = BY + hull[name][3] - hull[name][2]
+        if w > 256 or hgt > 256:
+            return None
+        box[name] = (w, hgt, per16)
+        foff[name] = slot_bytes
+        slot_bytes += (w * hgt * item + 127) // 128 * 128
+    # prefetch distance: as deep as an 8-slot ring allows (a slot holds one level of EVERY field here)
+    span_max = max([max(max(v["dk"]) for v in keys.values()) - min(min(v["dk"]) for v in keys.values())
+                    for keys in an.ring if keys] + [0])
+    LEAD_T = max(2, min(int(os.environ.get("B200_COLFUSE_TMA_LEAD", "12")), 15 - span_max))
+    # per loop: the fields it streams, the K offsets, the ring depth
+    loops = []
+    ring_bytes = 0
+    for n, (loop, secs, backward) in enumerate(run_loops):
+        keys = an.ring[n]
+        if not keys:
+            loops.append(None)
+            continue
+        dkmin = min(min(v["dk"]) for v in keys.values())
+        dkmax = max(max(v["dk"]) for v in keys.values())
+        span = dkmax - dkmin
+        depth = pow2ceil(span + LEAD_T + 1)
+        if depth > 16:
+            return None
+        names = sorted({k_[0] for k_ in keys})
+        loops.append({"dkmin": dkmin, "dkmax": dkmax, "span": span, "depth": depth, "fields": names,
+                      "tx": sum(box[nm][0] * box[nm][1] * size_of[ct_of(nm)] for nm in names)})
+    # ONE ring depth for every loop of the kernel: the barriers' phases follow the CTA-wide stream position cf_mb, so
+    # position -> (slot, parity) must be the same function in every loop
+    depth_all = max(lp["depth"] for lp in loops if lp is not None)
+    for lp in loops:
+        if lp is not None:
+            lp["depth"] = depth_all
+    ring_bytes = depth_all * slot_bytes
+
+    def guard_text(h):
+        e = block_ext[id(h)]
+        return f"i >= {e[0][0]} && i < a.ni + ({e[0][1]}) && j >= {e[1][0]} && j < a.nj + ({e[1][1]})"
+
+    guards: Dict[int, str] = {}
+    by_text: Dict[str, str] = {}
+    G = []
+    for h in all_h:
+        text = guard_text(h)
+        if text not in by_text:
+            by_text[text] = f"g{len(by_text)}"
+            G.append(f"        const bool {by_text[text]} = live && {text};")
+        guards[id(h)] = by_text[text]
+
+    S = []
+    S.append("    constexpr bool U = true;")
+    S.append("    typedef int idx_t;")
+    for name in (str(f) for f in fields if str(f) in gen.readonly):
+        S.append(f"    const {ct_of(name)} *__restrict__ g_{name} = a.{name}; (void)g_{name};")
+    S.append("    extern __shared__ __align__(1024) unsigned char b200_smem[];")
+    S.append("    __shared__ unsigned cf_tmem_slot;")
+    S.append("    __shared__ __align__(8) unsigned long long cf_full[16], cf_empty[16];")
+    S.append("    const int tid = (int)(threadIdx.y * blockDim.x + threadIdx.x);")
+    S.append(f"    if (tid == 0) {{ for (int s = 0; s < 16; ++s) {{ b200_mbar_init(&cf_full[s], 1); b200_mbar_init(&cf_empty[s], {T // 32}); }} }}")
+    S.append("    b200_stack cf_stk;")
+    S.append(f"    cf_stk.n_tmem = {NT};")
+    S.append(f"    cf_stk.cta = {T};")
+    S.append(f"    cf_stk.tmem = b200_stack_setup(&cf_tmem_slot, {NT});  // (its __syncthreads() also publishes the barriers)")
+    S.append(f"    cf_stk.smem = reinterpret_cast<double *>(b200_smem + {ring_bytes}) + tid;")
+    S.append(f"    cf_stk.n_smem = a.cf_{kname}_smem;")
+    S.append(f"    cf_stk.nthreads = (long long)gridDim.x * {T};")
+    S.append(f"    cf_stk.spill = a.cf_{kname}_spill + (long long)blockIdx.x * {T} + tid;")
+    S.append(f"    const int cf_tiles_i = (a.ni + ({ihi - ilo}) + {BX - 1}) / {BX};")
+    S.append(f"    const int cf_tiles = cf_tiles_i * ((a.nj + ({jhi - jlo}) + {BY - 1}) / {BY});")
+    S.append("    unsigned cf_mb = 0;  // position of the next loop's first level in the CTA's stream of ring slots")
+    S.append("    for (int cf_tile = (int)blockIdx.x; cf_tile < cf_tiles; cf_tile += (int)gridDim.x) {")
+    S.append(f"        const int ti0 = ({ilo}) + (cf_tile % cf_tiles_i) * {BX}, tj0 = ({jlo}) + (cf_tile / cf_tiles_i) * {BY};")
+    S.append("        const int i = ti0 + (int)threadIdx.x, j = tj0 + (int)threadIdx.y;")
+    S.append(f"        const bool live = i < a.ni + ({ihi}) && j < a.nj + ({jhi});")
+    S += G
+    for name in sorted(hull):  # the box starts on a 16-byte boundary of global memory (see lowering._tile_kernel)
+        S.append(f"        const int adj_{name} = (a.org_{name}[0] + ti0 + ({hull[name][0]})) & {box[name][2] - 1};")
+    for name in sorted(an.cached):
+        S.append(f"        {ct_of(name)} cur_{name} = 0, prev_{name} = 0;")
+    for n, (loop, secs, backward) in enumerate(run_loops):
+        step = -1 if backward else 1
+        lp = loops[n]
+        gen.cf_prev = 1 if backward else -1
+        gen.cf_ring = {}
+        S.append(f"        {{  // ---- vertical loop {n}: {'BACKWARD' if backward else 'FORWARD'}")
+        lo_all = L._interval_cond(secs[-1][0] if backward else secs[0][0])[0]
+        hi_all = L._interval_cond(secs[0][0] if backward else secs[-1][0])[1]
+        if lp is not None:
+            D, span = lp["depth"], lp["span"]
+            # the loop's level stream: position m holds level `start + step * m`, m = 0 .. nlev + span - 1
+            start = f"(({lo_all}) + ({lp['dkmin']}))" if not backward else f"(({hi_all}) - 1 + ({lp['dkmax']}))"
+            S.append(f"            const int cf_start = {start}, cf_nlev = ({hi_all}) - ({lo_all}), cf_npos = cf_nlev + {span};")
+            for q, key in enumerate(sorted(an.ring[n])):
+                name, di, dj = key
+                ct = ct_of(name)
+                w, hgt, per16 = box[name]
+                S.append(f"            const {ct} *const rq{q} = reinterpret_cast<const {ct} *>(b200_smem + {foff[name]}) + "
+                         f"((int)threadIdx.y + ({dj - hull[name][2]})) * {w} + ((int)threadIdx.x + ({di - hull[name][0]}) + adj_{name});"
+                         f"  // {name}[{di},{dj}]")
+                gen.cf_ring[key] = ((f"rq{q}", "cf_start", step), D - 1, slot_bytes // size_of[ct])
+            S.append("            auto cf_issue = [&](const int m) {  // thread 0: the boxes of stream position m")
+            S.append(f"                if (tid == 0 && m < cf_npos) {{")
+            S.append(f"                    const unsigned u = cf_mb + (unsigned)m, s = u & {D - 1}u;")
+            S.append(f"                    b200_mbar_wait(&cf_empty[s], ((u / {D}u) & 1u) ^ 1u);")
+            S.append(f"                    b200_mbar_expect_tx(&cf_full[s], {lp['tx']});")
+            S.append(f"                    const int lv = cf_start + ({step}) * m;")
+            for name in lp["fields"]:
+                S.append(f"                    b200_tma_load_3d(b200_smem + s * {slot_bytes} + {foff[name]}, a.tm_{kname}_{name}, "
+                         f"a.org_{name}[0] + ti0 + ({hull[name][0]}) - adj_{name}, a.org_{name}[1] + tj0 + ({hull[name][2]}), "
+                         f"a.org_{name}[2] + lv, &cf_full[s]);")
+            S.append("                }")
+            S.append("            };")
+            S.append("            auto cf_wait = [&](const int m) {  // every thread: position m has landed")
+            S.append(f"                const unsigned u = cf_mb + (unsigned)m; b200_mbar_wait(&cf_full[u & {D - 1}u], (u / {D}u) & 1u);")
+            S.append("            };")
+            S.append("            auto cf_done = [&](const int m) {  // this warp no longer reads position m")
+            S.append(f"                __syncwarp(); if ((tid & 31) == 0) b200_mbar_arrive(&cf_empty[(cf_mb + (unsigned)m) & {D - 1}u]);")
+            S.append("            };")
+            S.append(f"            for (int m = 0; m < {span + LEAD_T}; ++m) cf_issue(m);  // prologue")
+            S.append(f"            for (int m = 0; m < {span}; ++m) cf_wait(m);")
+        pops, loads, pushes = sorted(an.pop[n]), sorted(an.load[n]), sorted(an.push[n])
+
+        def paired(todo, fmt2, fmt1):
+            out, todo = [], list(todo)
+            while todo:
+                a_name = todo.pop(0)
+                pa = pslot[a_name]
+                if (todo and pslot[todo[0]] == pa + 1 and pa % 2 == 0 and NP % 2 == 0
+                        and ct_of(a_name) == "double" and ct_of(todo[0]) == "double"):
+                    out.append(fmt2.format(s=f"k * {NP} + {pa}", a=a_name, b=todo.pop(0)))
+                else:
+                    out.append(fmt1.format(s=f"k * {NP} + {pa}", a=a_name))
+            return out
+
+        first = f"(({hi_all}) - 1)" if backward else f"({lo_all})"
+        for interval, hs in secs:
+            lo, hi = L._interval_cond(interval)
+            if backward:
+                S.append(f"            for (int k = ({hi}) - 1; k >= ({lo}); --k) {{")
+            else:
+                S.append(f"            for (int k = ({lo}); k < ({hi}); ++k) {{")
+            if lp is not None:
+                S.append(f"                const int cf_t = (k - {first}) * ({step});  // the level's number in the loop")
+                S.append(f"                cf_issue(cf_t + {lp['span'] + LEAD_T}); cf_wait(cf_t + {lp['span']});")
+            if pops:
+                S.append("                __syncwarp();")
+                S += paired(pops, "                b200_stack_pop2(cf_stk, {s}, cur_{a}, cur_{b});",
+                            "                cur_{a} = b200_stack_pop(cf_stk, {s});")
+            for name in loads:
+                (rq, start_, step_), mask_, stride_ = gen.cf_ring[(name, 0, 0)]  # (the cached name itself reads cur_<f>)
+                S.append(f"                cur_{name} = {rq}[((cf_mb + ((k) - ({start_})) * ({step_})) & {mask_}) * {stride_}];")
+            for h in hs:
+                S.append(f"                if ({guards[id(h)]}) {{")
+                for d in L._declarations(h):
+                    S.append(" " * 20 + f"{L.CTYPES[d.dtype]} {d.name} = 0;")
+                S += gen.stmts(h.body, 20)
+                S.append("                }")
+            if pushes:
+                S.append("                __syncwarp();")
+                S += paired(pushes, "                b200_stack_push2(cf_stk, {s}, cur_{a}, cur_{b});",
+                            "                b200_stack_push(cf_stk, {s}, cur_{a});")
+            for name in sorted(an.reads_prev[n]):
+                S.append(f"                prev_{name} = cur_{name};")
+            if lp is not None:
+                S.append("                cf_done(cf_t);")
+            S.append("            }")
+        if lp is not None:
+            S.append(f"            for (int m = 0; m < {lp['span']}; ++m) cf_done(cf_nlev + m);  // the positions only read ahead")
+            S.append("            cf_mb += (unsigned)cf_npos;")
+        if pushes:
+            S.append("            b200_stack_fence();")
+        S.append("        }")
+    S.append("    }")
+    S.append("    b200_stack_teardown(&cf_tmem_slot);")
+    gen.cf_ring, gen.cf_cached = {}, {}
+    src = [f"__device__ __forceinline__ void {kname}_tma_impl(const Args &a)", "{"] + S + ["}",
+           f'extern "C" __global__ void __launch_bounds__({BX * BY}, 1) {kname}_t(const Args a) {{ {kname}_tma_impl(a); }}']
+    tma = {"smem_bytes": int(ring_bytes), "fields": {nm: [int(box[nm][0]), int(box[nm][1]), 1] for nm in sorted(hull)}}
+    return "\n".join(src), tma
 
 
 def _full_range(secs, backward: bool) -> bool:

@@ -243,7 +243,7 @@ def _host_source(src: str, plan) -> str:
     body = body.replace("#include <cstdint>\n#include <cmath>\n", "", 1)
     # the <k>_t entry points (TMA-staged inputs) are device-only
     body = re.sub(r"__device__ __forceinline__ void (\w+)_tma_impl\(const Args &a\).*?\n"
-                  r"extern \"C\" __global__ void __launch_bounds__\(\d+\) \1_t\(const Args a\)[^\n]*\n?", "", body,
+                  r"extern \"C\" __global__ void __launch_bounds__\([\d, ]+\) \1_t\(const Args a\)[^\n]*\n?", "", body,
                   flags=re.S)
     body = re.sub(r"extern __shared__ __align__\(\d+\) unsigned char b200_smem\[\];",
                   "unsigned char *b200_smem = emu_smem;", body)

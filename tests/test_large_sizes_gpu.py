@@ -109,6 +109,23 @@ def test_generated_kernel_at_a_size_that_crosses_boundaries(name):
         assert first.endswith(suffix), type(impl)._last_entry_points
 
 
+@pytest.mark.parametrize("name,domain", [("vertical_advection_dycore", (300, 131, 80)), ("tridiagonal_solver", (257, 66, 80)),
+                                         ("column_physics", (300, 200, 64))])
+def test_fused_column_kernel_with_tma_fed_rings(name, domain, monkeypatch):
+    """The `<k>_t` entry point of the fused column template (lowering_colfuse.TMA_RINGS, off by default): prefetch rings
+    fed by TMA tile loads issued by one thread of the CTA, completion on an mbarrier per slot.  K offsets (vadv reads
+    k - 1 .. k + 1), an I offset (wcon at i + 1), several tiles per CTA; bit-exact against the reference."""
+    mk, gtscript, gt_storage = _setup()
+    from gt4py_b200 import lowering_colfuse
+
+    monkeypatch.setattr(lowering_colfuse, "TMA_RINGS", True)
+    fn, ext = mk.definitions()[name][:2]
+    impl = _compare(gtscript, gt_storage, mk, name + "_tma", fn, ext, {"use_library_kernels": False}, {}, domain, seed=41)
+    assert "tma" in impl._plan_["kernels"][0]
+    if not EMU:
+        assert type(impl)._last_entry_points == ["k0_0_t"]
+
+
 @pytest.mark.parametrize("nk", [3, 64, 65, 111, 200])
 def test_fused_column_kernel_over_column_depths(nk):
     """Generated vadv with other externals (BET_M = 0.4: not the library's kernel) through the fused FORWARD / BACKWARD
