@@ -187,6 +187,20 @@ def emit(kname: str, unit, block_ext, fields, field_ext, scalar_names, locals_, 
     ctype = {n: L.CTYPES[fields[n]["dtype"]] for n in list(temps) + inputs}
 
     has_while = any(isinstance(node, oir.While) for _, h in unit for node in h.walk_values())
+    # horizontal regions that hang on the west / east edge of the domain (FV3-style edge and corner forms): a warp whose
+    # columns stay EDGE_W / EDGE_E columns away from those edges runs a copy of the loop without them
+    EDGE_W = EDGE_E = 0
+    n_edge = 0
+    for _, h in unit:
+        for node in h.walk_values():
+            if isinstance(node, oir.HorizontalRestriction):
+                el = L.edge_local(node.mask.i)
+                if el is not None:
+                    n_edge += 1
+                    if el[0] == "start":
+                        EDGE_W = max(EDGE_W, el[1])
+                    else:
+                        EDGE_E = max(EDGE_E, el[1])
     # horizontal executions that touch global memory themselves (a write to an API field, a read of a field that is not
     # kept in register windows): they keep their guard everywhere; the others only produce register values, which a
     # lane or row outside the execution's range may compute freely -- nothing valid ever reads them
@@ -221,7 +235,7 @@ def emit(kname: str, unit, block_ext, fields, field_ext, scalar_names, locals_, 
             S.append(f"    {{ const int i = min(max(ic0 + x0 + {c}, {lo_i}), a.ni + ({hi_i}) - 1), j = 0; "
                      f"p_{name}_{c} = g_{name} + ({gen._index(name, common.CartesianOffset.zero(), None)}); }}")
 
-    def loop(fast: bool) -> List[str]:
+    def loop(fast: bool, inner: bool = False) -> List[str]:
         """The J march; `fast`: every column of the warp is inside the domain, and only the horizontal executions that
         touch global memory themselves are guarded."""
         def issue(row: str, slot_const: int, ind: int) -> List[str]:
@@ -294,6 +308,7 @@ def emit(kname: str, unit, block_ext, fields, field_ext, scalar_names, locals_, 
                         if writer[name] == n:
                             m[(name, 0, 0)] = f"w_{name}_{(u - lag[n]) % depth[name]}_{c}"
                     maps.append(m)
+                gen.drop_edge_regions = inner
                 for c in range(C):
                     gen.march = maps[c]
                     B.append(f"                {{  // column {c}")
@@ -319,6 +334,7 @@ def emit(kname: str, unit, block_ext, fields, field_ext, scalar_names, locals_, 
                         B.append("                    }")
                     B.append("                }")
                 gen.march = None
+                gen.drop_edge_regions = False
                 B.append("            }")
             loads = [f"            const {ctype[name]} {var} = rg_{name}_{sc}["
                      + (f"((tb + ({u + ro})) & {RD - 1}) * {T}];" if not STATIC else f"{((u + ro) % RD) * T}];")
@@ -333,6 +349,11 @@ def emit(kname: str, unit, block_ext, fields, field_ext, scalar_names, locals_, 
     if has_while:  # (a `while` on a value no result depends on might not terminate)
         S += loop(False)
     else:
+        if n_edge:
+            S.append(f"    if (ic0 + ({ILOa}) >= {EDGE_W} && ic0 + ({ILOa}) + {32 * C} <= a.ni - ({EDGE_E})) {{"
+                     "  // ... and away from the west / east edge regions")
+            S += ["    " + ln for ln in loop(True, True)]
+            S.append("    } else")
         S.append(f"    if (ic0 + {WO} <= a.ni) {{  // every column of the warp's block is inside the domain")
         S += ["    " + ln for ln in loop(True)]
         S.append("    } else {")
