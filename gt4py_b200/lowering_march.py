@@ -81,10 +81,6 @@ def emit(kname: str, unit, block_ext, fields, field_ext, scalar_names, locals_, 
     stages = L._tile_stages(unit, smem_names)
     temps = {str(x) for x in smem_names}
     readonly = L._readonly_globals(unit, smem_names, fields)
-    stage_of: Dict[int, int] = {}
-    for n, stage in enumerate(stages):
-        for _, h in stage:
-            stage_of[id(h)] = n
     # ---- who writes / reads what, where -------------------------------------------------------------------------
     writer: Dict[str, int] = {}
     reads: Dict[str, List[Tuple[int, int, int]]] = {}      # temp or staged input -> [(stage, di, dj)]
