@@ -21,7 +21,7 @@ Numbers on the JSON line
   kernels      the same for both kernels of the step.
   configs      (N = 1) driver-visible timings + rooflines of the other BASELINE configs: [2] hdiff + vadv at
                1024x1024x80 (the north star's single-GPU target), [3] the FV3-style chain at 512x512x128 (generated
-               fused tile kernel, 32 B/point), [1] vadv 256x256x80, [0] hdiff 128x128x80, and the Thomas solver
+               fused kernel, 32 B/point), [1] vadv 256x256x80, [0] hdiff 128x128x80, and the Thomas solver
                (a3, 56 B/point) at 1024x1024x80.
   parity       after the timed region: two steps of a small model whose exchanged fields CHANGE every step (hdiff
                feeds its own output back, vadv's result becomes the next wcon), every received halo cell poisoned
