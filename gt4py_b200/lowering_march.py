@@ -207,10 +207,26 @@ def emit(kname: str, unit, block_ext, fields, field_ext, scalar_names, locals_, 
 
     S: List[str] = []
     S.append("    const int lane = (int)(threadIdx.x & 31u);")
-    S.append(f"    const int ic0 = ((int)blockIdx.x * {WARPS} + (int)(threadIdx.x >> 5)) * {WO};  // the warp's first result column")
+    # the last warp of a row would hang over the east end of the domain and take the guarded loop (twice the
+    # instructions): it is moved west until its block ends at the domain's last column -- it then recomputes a few
+    # columns of its neighbour and writes the same values there.  Only when no global field is read AND written by the
+    # kernel (a second execution of `x = x + ...` would not be the same write).
+    rw_global = False
+    g_reads, g_writes = set(), set()
+    for _, h in unit:
+        for nm, _di, _dj, _dk, is_write in _field_accesses(h):
+            if nm not in temps:
+                (g_writes if is_write else g_reads).add(nm)
+    rw_global = bool(g_reads & g_writes)
+    S.append(f"    const int ic_raw = ((int)blockIdx.x * {WARPS} + (int)(threadIdx.x >> 5)) * {WO};")
+    if rw_global:
+        S.append("    const int ic0 = ic_raw;  // the warp's first result column")
+    else:
+        S.append(f"    const int ic0 = (ic_raw + {WO} > a.ni && a.ni >= {WO} && ic_raw < a.ni) ? a.ni - {WO} : ic_raw;"
+                 "  // the warp's first result column")
     S.append(f"    const int x0 = lane * {C} + ({ILOa});                 // this lane's first column, relative to ic0")
     S.append(f"    const int tj0 = (int)blockIdx.y * {STRIP}, k = (int)blockIdx.z;")
-    S.append("    if (ic0 >= a.ni) return;  // (the whole warp: no lane is left behind at a shuffle)")
+    S.append("    if (ic_raw >= a.ni) return;  // (the whole warp: no lane is left behind at a shuffle)")
     # iterations of this strip: none once every stage is past the last row it computes (a short last strip)
     S.append(f"    const int nit = min({NIT}, a.nj + ({XR}) - (tj0 + ({R0})));")
     for name in windows:
