@@ -605,7 +605,8 @@ static int launch(Plan &p, const int64_t dom[3], const b200_field *fields, int n
                 if (m.kind == M_CF_SPILL) put<void *>(p, m.offset, k.spill);
                 if (m.kind == M_CF_SMEM) put<int32_t>(p, m.offset, (int32_t)n_smem);
             }
-            block[0] = (uint32_t)k.bx; block[1] = (uint32_t)k.by; block[2] = 1;
+            // (the <k>_t entry runs with one more row of threads: the producer of its TMA rings, lowering_colfuse._emit_tma)
+            block[0] = (uint32_t)k.bx; block[1] = (uint32_t)(k.by + (entry == k.entry_t && k.entry_t ? 1 : 0)); block[2] = 1;
             grid[0] = (uint32_t)ctas; grid[1] = 1; grid[2] = 1;
         } else {
             block[0] = 32; block[1] = 4; block[2] = 1;

@@ -430,7 +430,8 @@ class GeneratedStencil(StencilObject):
                 spill = self._cf_spill(k["name"], (need - n_smem) * ctas * bx * by * 8, stream)
                 setattr(a, f"cf_{k['name']}_smem", n_smem)
                 setattr(a, f"cf_{k['name']}_spill", spill)
-                block, grid = (bx, by, 1), (ctas, 1, 1)
+                # (the <k>_t entry runs with one more row of threads: the producer of its TMA rings)
+                block, grid = (bx, by + (1 if sfx == "_t" else 0), 1), (ctas, 1, 1)
             else:
                 bx, by = _COLUMN_BLOCK
                 block, grid = (bx, by, 1), ((wi + bx - 1) // bx, (wj + by - 1) // by, 1)

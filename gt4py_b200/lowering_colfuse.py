@@ -35,11 +35,13 @@ LEAD = int(os.environ.get("B200_COLFUSE_LEAD", "6"))
 # cp.async copies), not by the latency the second chain would hide; kept for parts where that differs, with a test.
 PIPELINE = os.environ.get("B200_COLFUSE_PIPELINE", "0") != "0"
 MIDPATH = os.environ.get("B200_COLFUSE_MIDPATH", "1") != "0"
-# third entry point <k>_t: prefetch rings fed by TMA tile loads issued by one thread (see _emit_tma).  OFF by default, by
-# measurement (B200, 1024x1024x80, profiles/r2_colfuse_tma.jsonl): bit-exact, but vadv 2.04 ms against 0.90 ms with the
-# per-thread cp.async rings, Thomas solver 1.42 against 0.90, whatever the ring depth (8 or 16 slots) -- ncu: 30 % of all
-# stall samples sit in the loops that wait for a slot's `full` barrier, 587 M executed warp instructions against 200 M:
-# one level of boxes per slot issued from inside a consumer warp does not keep the rings ahead of 8 consumer warps.
+# third entry point <k>_t: prefetch rings fed by TMA tile loads issued by a producer lane (see _emit_tma).  OFF by default,
+# by measurement (B200, 1024x1024x80, profiles/r2_colfuse_tma.jsonl): bit-exact, but vadv 1.25 ms against 0.90 ms with the
+# per-thread cp.async rings, Thomas solver 1.01 against 0.90, column_physics 0.64-0.69 against 0.59, with 8 or 16 slots.
+# (First form, thread 0 of the consumers issuing from inside the level loop: 2.04 / 1.42 / 1.00 ms -- the rings starved.)
+# ncu on the producer-row form: the ring is not starved (9 % of the stall samples on try_wait results), but a level's
+# barrier test + arrive cost the instructions its five cp.async did (538 M against 511 M warp instructions) and the
+# try_wait round trip is on every warp's critical path once per level: 550 cycles per level and CTA against 392.
 TMA_RINGS = os.environ.get("B200_COLFUSE_TMA", "0") != "0"
 assert (BX * BY) % 128 == 0 and BX * BY <= 1024, "a fused column CTA is a whole number of 4-warp groups"
 
@@ -464,12 +466,15 @@ def emit(kname: str, stencil: oir.Stencil, run: List[int], units_by_loop, block_
 
 def _emit_tma(kname, run_loops, an, block_ext, fields, scalar_names, L):
     """Third entry point `<k>_t` of a fused column kernel: the prefetch rings are fed by TMA tile loads (one box per
-    field and level, issued by ONE thread of the CTA, completion on an mbarrier per ring slot) instead of one cp.async
-    per thread, field and level -- the copies are a quarter of the instructions of a level in the `_u` form.  Same
-    persistent-tile / value-stack structure.  Every thread waits on the slot's `full` barrier before it reads a level;
-    one lane per warp arrives on its `empty` barrier when the warp is done with it; the issuing thread (thread 0) runs
-    LEAD levels ahead inside the level loop, so no warp is set aside as a producer.  Levels and columns outside a field
-    are zero-filled by the hardware (never read: extent analysis).  Returns (source, tma meta) or None."""
+    field and level, completion on an mbarrier per ring slot) instead of one cp.async per thread, field and level -- the
+    copies are a quarter of the instructions of a level in the `_u` form.  Same persistent-tile / value-stack structure
+    for the BX x BY consumer threads; the CTA is launched with ONE MORE ROW of threads (block BX x (BY + 1)), whose
+    first lane is the producer: it walks the same tiles, loops and levels as the consumers and issues the boxes of the
+    CTA's whole level stream, position after position, held back only by the slots' `empty` barriers -- so the ring
+    stays full across loop and tile boundaries (the `_u` form drains and refills it at each).  Every consumer waits on
+    a slot's `full` barrier before it reads a level; one lane per warp arrives on its `empty` barrier when the warp is
+    done with it.  Levels and columns outside a field are zero-filled by the hardware (never read: extent analysis).
+    Returns (source, tma meta) or None."""
     size_of = {"double": 8, "float": 4, "int64_t": 8, "int32_t": 4}
 
     def ct_of(name):
@@ -509,10 +514,8 @@ def _emit_tma(kname, run_loops, an, block_ext, fields, scalar_names, L):
         box[name] = (w, hgt, per16)
         foff[name] = slot_bytes
         slot_bytes += (w * hgt * item + 127) // 128 * 128
-    # prefetch distance: as deep as an 8-slot ring allows (a slot holds one level of EVERY field here)
-    span_max = max([max(max(v["dk"]) for v in keys.values()) - min(min(v["dk"]) for v in keys.values())
-                    for keys in an.ring if keys] + [0])
-    LEAD_T = max(2, min(int(os.environ.get("B200_COLFUSE_TMA_LEAD", "12")), 15 - span_max))
+    # ring slots (a slot holds one level of EVERY field here): a power of two, at least the K span of the reads + 2
+    SLOTS = int(os.environ.get("B200_COLFUSE_TMA_SLOTS", "8"))
     # per loop: the fields it streams, the K offsets, the ring depth
     loops = []
     ring_bytes = 0
@@ -524,7 +527,7 @@ def _emit_tma(kname, run_loops, an, block_ext, fields, scalar_names, L):
         dkmin = min(min(v["dk"]) for v in keys.values())
         dkmax = max(max(v["dk"]) for v in keys.values())
         span = dkmax - dkmin
-        depth = pow2ceil(span + LEAD_T + 1)
+        depth = max(pow2ceil(span + 2), pow2ceil(SLOTS))
         if depth > 16:
             return None
         names = sorted({k_[0] for k_ in keys})
@@ -572,14 +575,42 @@ def _emit_tma(kname, run_loops, an, block_ext, fields, scalar_names, L):
     S.append(f"    cf_stk.spill = a.cf_{kname}_spill + (long long)blockIdx.x * {T} + tid;")
     S.append(f"    const int cf_tiles_i = (a.ni + ({ihi - ilo}) + {BX - 1}) / {BX};")
     S.append(f"    const int cf_tiles = cf_tiles_i * ((a.nj + ({jhi - jlo}) + {BY - 1}) / {BY});")
+    tile_head = ["    for (int cf_tile = (int)blockIdx.x; cf_tile < cf_tiles; cf_tile += (int)gridDim.x) {",
+                 f"        const int ti0 = ({ilo}) + (cf_tile % cf_tiles_i) * {BX}, tj0 = ({jlo}) + (cf_tile / cf_tiles_i) * {BY};"]
+    for name in sorted(hull):  # the box starts on a 16-byte boundary of global memory (see lowering._tile_kernel)
+        tile_head.append(f"        const int adj_{name} = (a.org_{name}[0] + ti0 + ({hull[name][0]})) & {box[name][2] - 1};")
+    # ---- the producer: thread (0, BY) of the block
+    P = ["    unsigned cf_u = 0;  // position in the CTA's stream of ring slots"] + tile_head
+    for n, (loop, secs, backward) in enumerate(run_loops):
+        lp = loops[n]
+        if lp is None:
+            continue
+        step = -1 if backward else 1
+        lo_all = L._interval_cond(secs[-1][0] if backward else secs[0][0])[0]
+        hi_all = L._interval_cond(secs[0][0] if backward else secs[-1][0])[1]
+        D = lp["depth"]
+        start = f"(({lo_all}) + ({lp['dkmin']}))" if not backward else f"(({hi_all}) - 1 + ({lp['dkmax']}))"
+        P.append(f"        {{  // ---- vertical loop {n}: position m of its stream holds level cf_start {'-' if backward else '+'} m")
+        P.append(f"            const int cf_start = {start}, cf_npos = ({hi_all}) - ({lo_all}) + {lp['span']};")
+        P.append("            for (int m = 0; m < cf_npos; ++m, ++cf_u) {")
+        P.append(f"                const unsigned s = cf_u & {D - 1}u;")
+        P.append(f"                b200_mbar_wait(&cf_empty[s], ((cf_u / {D}u) & 1u) ^ 1u);")
+        P.append(f"                b200_mbar_expect_tx(&cf_full[s], {lp['tx']});")
+        P.append(f"                const int lv = cf_start + ({step}) * m;")
+        for name in lp["fields"]:
+            P.append(f"                b200_tma_load_3d(b200_smem + s * {slot_bytes} + {foff[name]}, a.tm_{kname}_{name}, "
+                     f"a.org_{name}[0] + ti0 + ({hull[name][0]}) - adj_{name}, a.org_{name}[1] + tj0 + ({hull[name][2]}), "
+                     f"a.org_{name}[2] + lv, &cf_full[s]);")
+        P.append("            }")
+        P.append("        }")
+    P.append("    }")
+    # ---- the consumers
+    head_at = len(S)
     S.append("    unsigned cf_mb = 0;  // position of the next loop's first level in the CTA's stream of ring slots")
-    S.append("    for (int cf_tile = (int)blockIdx.x; cf_tile < cf_tiles; cf_tile += (int)gridDim.x) {")
-    S.append(f"        const int ti0 = ({ilo}) + (cf_tile % cf_tiles_i) * {BX}, tj0 = ({jlo}) + (cf_tile / cf_tiles_i) * {BY};")
+    S += tile_head
     S.append("        const int i = ti0 + (int)threadIdx.x, j = tj0 + (int)threadIdx.y;")
     S.append(f"        const bool live = i < a.ni + ({ihi}) && j < a.nj + ({jhi});")
     S += G
-    for name in sorted(hull):  # the box starts on a 16-byte boundary of global memory (see lowering._tile_kernel)
-        S.append(f"        const int adj_{name} = (a.org_{name}[0] + ti0 + ({hull[name][0]})) & {box[name][2] - 1};")
     for name in sorted(an.cached):
         S.append(f"        {ct_of(name)} cur_{name} = 0, prev_{name} = 0;")
     for n, (loop, secs, backward) in enumerate(run_loops):
@@ -603,25 +634,12 @@ def _emit_tma(kname, run_loops, an, block_ext, fields, scalar_names, L):
                          f"((int)threadIdx.y + ({dj - hull[name][2]})) * {w} + ((int)threadIdx.x + ({di - hull[name][0]}) + adj_{name});"
                          f"  // {name}[{di},{dj}]")
                 gen.cf_ring[key] = ((f"rq{q}", "cf_start", step), D - 1, slot_bytes // size_of[ct])
-            S.append("            auto cf_issue = [&](const int m) {  // thread 0: the boxes of stream position m")
-            S.append(f"                if (tid == 0 && m < cf_npos) {{")
-            S.append(f"                    const unsigned u = cf_mb + (unsigned)m, s = u & {D - 1}u;")
-            S.append(f"                    b200_mbar_wait(&cf_empty[s], ((u / {D}u) & 1u) ^ 1u);")
-            S.append(f"                    b200_mbar_expect_tx(&cf_full[s], {lp['tx']});")
-            S.append(f"                    const int lv = cf_start + ({step}) * m;")
-            for name in lp["fields"]:
-                S.append(f"                    b200_tma_load_3d(b200_smem + s * {slot_bytes} + {foff[name]}, a.tm_{kname}_{name}, "
-                         f"a.org_{name}[0] + ti0 + ({hull[name][0]}) - adj_{name}, a.org_{name}[1] + tj0 + ({hull[name][2]}), "
-                         f"a.org_{name}[2] + lv, &cf_full[s]);")
-            S.append("                }")
-            S.append("            };")
             S.append("            auto cf_wait = [&](const int m) {  // every thread: position m has landed")
             S.append(f"                const unsigned u = cf_mb + (unsigned)m; b200_mbar_wait(&cf_full[u & {D - 1}u], (u / {D}u) & 1u);")
             S.append("            };")
             S.append("            auto cf_done = [&](const int m) {  // this warp no longer reads position m")
             S.append(f"                __syncwarp(); if ((tid & 31) == 0) b200_mbar_arrive(&cf_empty[(cf_mb + (unsigned)m) & {D - 1}u]);")
             S.append("            };")
-            S.append(f"            for (int m = 0; m < {span + LEAD_T}; ++m) cf_issue(m);  // prologue")
             S.append(f"            for (int m = 0; m < {span}; ++m) cf_wait(m);")
         pops, loads, pushes = sorted(an.pop[n]), sorted(an.load[n]), sorted(an.push[n])
 
@@ -646,7 +664,7 @@ def _emit_tma(kname, run_loops, an, block_ext, fields, scalar_names, L):
                 S.append(f"            for (int k = ({lo}); k < ({hi}); ++k) {{")
             if lp is not None:
                 S.append(f"                const int cf_t = (k - {first}) * ({step});  // the level's number in the loop")
-                S.append(f"                cf_issue(cf_t + {lp['span'] + LEAD_T}); cf_wait(cf_t + {lp['span']});")
+                S.append(f"                cf_wait(cf_t + {lp['span']});")
             if pops:
                 S.append("                __syncwarp();")
                 S += paired(pops, "                b200_stack_pop2(cf_stk, {s}, cur_{a}, cur_{b});",
@@ -676,11 +694,21 @@ def _emit_tma(kname, run_loops, an, block_ext, fields, scalar_names, L):
             S.append("            b200_stack_fence();")
         S.append("        }")
     S.append("    }")
+    body = S[head_at:]
+    S = S[:head_at]
+    S.append(f"    if (tid >= {T}) {{  // the extra row of threads: its first lane feeds the rings")
+    S.append(f"        if (tid == {T}) {{")
+    S += ["    " * 2 + line for line in P]
+    S.append("        }")
+    S.append("    } else {")
+    S += ["    " + line for line in body]
+    S.append("    }")
     S.append("    b200_stack_teardown(&cf_tmem_slot);")
     gen.cf_ring, gen.cf_cached = {}, {}
     src = [f"__device__ __forceinline__ void {kname}_tma_impl(const Args &a)", "{"] + S + ["}",
-           f'extern "C" __global__ void __launch_bounds__({BX * BY}, 1) {kname}_t(const Args a) {{ {kname}_tma_impl(a); }}']
-    tma = {"smem_bytes": int(ring_bytes), "fields": {nm: [int(box[nm][0]), int(box[nm][1]), 1] for nm in sorted(hull)}}
+           f'extern "C" __global__ void __launch_bounds__({BX * (BY + 1)}, 1) {kname}_t(const Args a) {{ {kname}_tma_impl(a); }}']
+    tma = {"smem_bytes": int(ring_bytes), "producer_rows": 1,
+           "fields": {nm: [int(box[nm][0]), int(box[nm][1]), 1] for nm in sorted(hull)}}
     return "\n".join(src), tma
 
 

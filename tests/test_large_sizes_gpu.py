@@ -113,7 +113,7 @@ def test_generated_kernel_at_a_size_that_crosses_boundaries(name):
                                          ("column_physics", (300, 200, 64))])
 def test_fused_column_kernel_with_tma_fed_rings(name, domain, monkeypatch):
     """The `<k>_t` entry point of the fused column template (lowering_colfuse.TMA_RINGS, off by default): prefetch rings
-    fed by TMA tile loads issued by one thread of the CTA, completion on an mbarrier per slot.  K offsets (vadv reads
+    fed by TMA tile loads issued by a producer lane in an extra row of threads, completion on an mbarrier per slot.  K offsets (vadv reads
     k - 1 .. k + 1), an I offset (wcon at i + 1), several tiles per CTA; bit-exact against the reference."""
     mk, gtscript, gt_storage = _setup()
     from gt4py_b200 import lowering_colfuse
