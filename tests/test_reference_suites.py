@@ -12,6 +12,9 @@ oracle/_ref (made by oracle/make_ref.py, travels to the GPU box), selected with 
   storage_tests/unit_tests/test_interface.py          gt4py.storage.* for the name
   multi_feature_tests/test_code_generation.py         70 feature stencils built and run
   multi_feature_tests/test_suites.py                  40 StencilTestSuite classes through the Hypothesis harness
+  feature_tests/test_stencil_object.py                stencil object attributes / repeated calls for the name
+  multi_feature_tests/test_math_functions.py          every unary / binary native function against NumPy
+  unit_tests/test_lazy_stencil.py                     LazyStencil: build on first use, field_info / call through it
 
 ``-m gpu``: on the B200 through libgt4py_b200.so (cupy is absent from the image: oracle/ref_shims_gpu holds a stand-in
 built on DeviceArray that the TESTS use as their array library).  CPU suite: the same modules against the host
@@ -40,6 +43,9 @@ MODULES = [
     "storage_tests/unit_tests/test_interface.py",
     f"{CT}/integration_tests/multi_feature_tests/test_code_generation.py",
     f"{CT}/integration_tests/multi_feature_tests/test_suites.py",
+    f"{CT}/integration_tests/feature_tests/test_stencil_object.py",
+    f"{CT}/integration_tests/multi_feature_tests/test_math_functions.py",
+    f"{CT}/unit_tests/test_lazy_stencil.py",
 ]
 #: tests of pass 2: parametrised over CPU_BACKENDS in the reference, backend-agnostic in what they assert
 AS_CPU_MODULES = [f"{CT}/integration_tests/feature_tests/test_call_interface.py"]
@@ -52,7 +58,7 @@ EXPECTED_FAILURES = {
 }
 
 #: what must at least have run (guards against a silently empty selection)
-MINIMUM = {"pass1": 190, "pass2": 3}
+MINIMUM = {"pass1": 197, "pass2": 3}
 
 
 def run_reference_tests(modules, tag, emu, as_cpu=False, workers=6, extra=()):
