@@ -17,7 +17,7 @@ lap-of-lap diffusion, hdiff) is lowered to ONE kernel in which every temporary l
     the inputs into register windows ahead of use; ncu showed half of all stall samples on the moves of those loaded
     values -- ptxas consumed them at once -- and 43 % issue utilisation; with the ring: 76 %.)
   * the halo of the extent analysis (passes/oir_optimizations/utils.py:293-330) is recomputed per warp in I (26 of
-    32 columns are results for a total I halo of 6) and per strip in J; a lane or row outside a stage's range
+    32 columns -- 56 of 64 with two columns per lane -- are results for a total I halo of 6) and per strip in J; a lane or row outside a stage's range
     computes values nothing valid ever reads, so only the horizontal executions that touch global memory themselves
     are guarded (the copies clamp their address instead).
 
@@ -27,11 +27,17 @@ GridTools backends (gtc/passes/oir_optimizations/caches.py, IJCacheDetection) --
 here registers.
 
 Measured on B200 at 512 x 512 x 128 float64 (tools/make_march_variants.py + tools/chain_bench.py,
-profiles/r2_march_variants*.jsonl), ms per call, tile kernel -> this form with the defaults below (one column per lane,
+profiles/r2_march_variants*.jsonl), ms per call, tile kernel -> this form with its first defaults (one column per lane,
 4 warps per CTA, 80 registers, LEAD 2): config-4 chain 0.393 -> 0.322, lap-of-lap diffusion 0.195 -> 0.160, hdiff
 0.240 -> 0.174; two-stage upwind advection stays a tile kernel (0.163, at the HBM roofline; this form: 0.19).  It is
-now bound by instruction issue (7.6 warp instructions per point on the chain, of which 1.4 are float64 arithmetic):
-two columns per lane halve the shuffles but need 128 registers and measured slower (0.395 on the chain).
+then bound by instruction issue (7.6 warp instructions per point on the chain, of which 1.4 are float64 arithmetic),
+the shallow kernels by the shuffle / shared-memory pipe.  Two columns per lane halve the shuffles; with the first ring
+layout (one ring per column, two 8-byte copies and two LDS.64 per input row) they measured slower (0.395 on the chain).
+Since the pair of a lane is ONE 16-byte ring element (one cp.async and one LDS.128 per input row where the pair is
+whole and aligned in global memory -- every warp's first column is even, gt4py storages align the origin -- two plain
+copies into the same element otherwise) two columns per lane and 2 warps per CTA are the defaults
+(profiles/r2_march_pairs.jsonl, 512 x 512 x 128 / 1024 x 1024 x 80, one column -> two): chain 0.251 -> 0.248 / 0.599 ->
+0.551 ms, diffusion 0.155 -> 0.139 / 0.366 -> 0.314, hdiff 0.167 -> 0.168 / 0.387 -> 0.376.
 
 Not every unit qualifies (`emit` returns None and the tile kernel is used): every fused temporary must be written in
 ONE stage and read only by later stages (or at zero offset inside its own), and the kernel must have at least
@@ -73,10 +79,10 @@ def emit(kname: str, unit, block_ext, fields, field_ext, scalar_names, locals_, 
          ) -> Optional[Tuple[str, Dict[str, Any]]]:
     """(CUDA source, launch metadata) of the warp-march kernel of `unit`, or None if the unit does not qualify.
     `L` is the lowering module (ExprGen, CTYPES, helpers)."""
-    C = _knob("B200_MARCH_COLUMNS", 1)          # columns per lane
+    C = _knob("B200_MARCH_COLUMNS", 2)          # columns per lane
     STRIP = _knob("B200_MARCH_STRIP", 64)       # rows a warp marches over
     LEAD = _knob("B200_MARCH_LEAD", 2)          # rows an input is copied into the lane's shared-memory ring ahead of use
-    WARPS = _knob("B200_MARCH_WARPS", 4)        # warps per CTA (independent of each other: scheduling granularity only)
+    WARPS = _knob("B200_MARCH_WARPS", 2)        # warps per CTA (independent of each other: scheduling granularity only)
     MINB = _knob("B200_MARCH_MIN_BLOCKS", 0)    # __launch_bounds__ second argument (caps the registers per thread)
     stages = L._tile_stages(unit, smem_names)
     temps = {str(x) for x in smem_names}
@@ -155,6 +161,8 @@ def emit(kname: str, unit, block_ext, fields, field_ext, scalar_names, locals_, 
     IHI = max([e[1] for e in s_ext] + [e[1] for e in in_ext.values()])
     ILOa = -((-ILO + C - 1) // C * C)                  # first column of lane 0, relative to the warp's first result
     WO = 32 * C - (IHI - ILOa)                          # result columns per warp
+    if C == 2 and _knob("B200_MARCH_PAIRS", 1):
+        WO -= WO % 2                                    # (every warp's first column even: its lanes' pairs stay aligned)
     if WO < 8 * C:
         return None
     R0 = min([s_ext[n][2] + lag[n] for n in range(len(stages))] + [e[2] for e in in_ext.values()])
@@ -171,12 +179,16 @@ def emit(kname: str, unit, block_ext, fields, field_ext, scalar_names, locals_, 
     if STATIC:
         U = max(U, RD)
         NIT = (NIT + U - 1) // U * U
+    # two columns per lane: the pair is ONE ring element (16 / 8 bytes: one cp.async and one LDS.128 / LDS.64 per row
+    # where the pair is whole and aligned in global memory, two plain copies into the same element otherwise)
+    PAIR = C == 2 and bool(_knob("B200_MARCH_PAIRS", 1))
     ring_off: Dict[Tuple[str, int], int] = {}
     smem_bytes = 0
     for name in inputs:
         for c in range(C):
             ring_off[(name, c)] = smem_bytes
-            smem_bytes += RD * T * L.TMA_DTYPES[L.CTYPES[fields[name]["dtype"]]]
+            if not PAIR or c == C - 1:
+                smem_bytes += RD * T * L.TMA_DTYPES[L.CTYPES[fields[name]["dtype"]]] * (C if PAIR else 1)
 
     gen = L.ExprGen(fields, scalar_names, locals_, False, regs=regs)
     gen.readonly = readonly
@@ -234,7 +246,10 @@ def emit(kname: str, unit, block_ext, fields, field_ext, scalar_names, locals_, 
             S.append(f"    {ctype[name]} " + ", ".join(f"w_{name}_{q}_{c} = 0" for c in range(C)) + ";")
     if inputs:
         S.append("    extern __shared__ __align__(16) unsigned char b200_smem[];")
-    for name in inputs:  # slot s of this lane's ring: rg_<field>_<column>[s * T]
+    for name in inputs:  # slot s of this lane's ring: rg_<field>_<column>[s * T]  (pairs: rg_<field>[s * 2 T + column])
+        if PAIR:
+            S.append(f"    {ctype[name]} *rg_{name} = ({ctype[name]} *)(b200_smem + {ring_off[(name, 0)]}) + 2 * (int)threadIdx.x;")
+            continue
         for c in range(C):
             S.append(f"    {ctype[name]} *rg_{name}_{c} = ({ctype[name]} *)(b200_smem + {ring_off[(name, c)]}) + (int)threadIdx.x;")
     # Input rows are copied without a column guard: a lane whose column lies outside the range the stencil reads
@@ -246,6 +261,10 @@ def emit(kname: str, unit, block_ext, fields, field_ext, scalar_names, locals_, 
             S.append(f"    const {ctype[name]} *p_{name}_{c};")
             S.append(f"    {{ const int i = min(max(ic0 + x0 + {c}, {lo_i}), a.ni + ({hi_i}) - 1), j = 0; "
                      f"p_{name}_{c} = g_{name} + ({gen._index(name, common.CartesianOffset.zero(), None)}); }}")
+        if PAIR:  # both columns inside the field, adjacent in memory, the pair aligned in every row
+            pb = 2 * L.TMA_DTYPES[ctype[name]]
+            S.append(f"    const bool pr_{name} = p_{name}_1 == p_{name}_0 + 1 && ((unsigned long long)p_{name}_0 & {pb - 1}ull) == 0 "
+                     f"&& (a.{name}_s[1] & 1) == 0;")
 
     def loop(fast: bool, inner: bool = False) -> List[str]:
         """The J march; `fast`: every column of the warp is inside the domain, and only the horizontal executions that
@@ -259,8 +278,14 @@ def emit(kname: str, unit, block_ext, fields, field_ext, scalar_names, locals_, 
                 lo_i, hi_i, lo_j, hi_j = in_ext[name]
                 cp = "b200_cp_async8" if L.TMA_DTYPES[ctype[name]] == 8 else "b200_cp_async4"
                 out.append(" " * ind + f"{{ const int jl = min(max({row}, {lo_j}), a.nj + ({hi_j}) - 1);")
-                for c in range(C):
-                    out.append(" " * ind + f"  {cp}(rg_{name}_{c} + {sl} * {T}, p_{name}_{c} + (idx_t)jl * (idx_t)a.{name}_s[1], true);")
+                if PAIR:
+                    cp2 = "b200_cp_async16" if L.TMA_DTYPES[ctype[name]] == 8 else "b200_cp_async8"
+                    out.append(" " * ind + f"  if (pr_{name}) {cp2}(rg_{name} + {sl} * {2 * T}, p_{name}_0 + (idx_t)jl * (idx_t)a.{name}_s[1], true);")
+                    out.append(" " * ind + f"  else {{ {cp}(rg_{name} + {sl} * {2 * T}, p_{name}_0 + (idx_t)jl * (idx_t)a.{name}_s[1], true); "
+                               f"{cp}(rg_{name} + {sl} * {2 * T} + 1, p_{name}_1 + (idx_t)jl * (idx_t)a.{name}_s[1], true); }}")
+                else:
+                    for c in range(C):
+                        out.append(" " * ind + f"  {cp}(rg_{name}_{c} + {sl} * {T}, p_{name}_{c} + (idx_t)jl * (idx_t)a.{name}_s[1], true);")
                 out.append(" " * ind + "}")
             out.append(" " * ind + "b200_cp_commit();")
             return out
@@ -348,9 +373,19 @@ def emit(kname: str, unit, block_ext, fields, field_ext, scalar_names, locals_, 
                 gen.march = None
                 gen.drop_edge_regions = False
                 B.append("            }")
-            loads = [f"            const {ctype[name]} {var} = rg_{name}_{sc}["
-                     + (f"((tb + ({u + ro})) & {RD - 1}) * {T}];" if not STATIC else f"{((u + ro) % RD) * T}];")
-                     for (name, sc, ro), var in ring_loads.items()]
+            if PAIR:  # one 16- / 8-byte read per (input, row), then its halves
+                loads, seen = [], set()
+                for (name, sc, ro), var in ring_loads.items():
+                    if (name, ro) not in seen:
+                        seen.add((name, ro))
+                        at = f"((tb + ({u + ro})) & {RD - 1}) * {2 * T}" if not STATIC else f"{((u + ro) % RD) * 2 * T}"
+                        loads.append(f"            const b200_pair<{ctype[name]}> vp{u}_{name}_{'m' if ro < 0 else 'p'}{abs(ro)} = "
+                                     f"*reinterpret_cast<const b200_pair<{ctype[name]}> *>(rg_{name} + {at});")
+                    loads.append(f"            const {ctype[name]} {var} = vp{u}_{name}_{'m' if ro < 0 else 'p'}{abs(ro)}.{'xy'[sc]};")
+            else:
+                loads = [f"            const {ctype[name]} {var} = rg_{name}_{sc}["
+                         + (f"((tb + ({u + ro})) & {RD - 1}) * {T}];" if not STATIC else f"{((u + ro) % RD) * T}];")
+                         for (name, sc, ro), var in ring_loads.items()]
             B[top:top] = loads
             B.append("        }")
         B.append("    }")

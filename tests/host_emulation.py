@@ -81,6 +81,8 @@ static inline void emu_check_src(const void *src, size_t n)
 }
 static inline void b200_cp_async8(void *dst, const void *src, bool valid) { if (valid) { emu_check_src(src, 8); memcpy(dst, src, 8); } else memset(dst, 0, 8); }
 static inline void b200_cp_async4(void *dst, const void *src, bool valid) { if (valid) { emu_check_src(src, 4); memcpy(dst, src, 4); } else memset(dst, 0, 4); }
+static inline void b200_cp_async16(void *dst, const void *src, bool valid) { if (valid) { emu_check_src(src, 16); memcpy(dst, src, 16); } else memset(dst, 0, 16); }
+template <typename T> struct alignas(2 * sizeof(T)) b200_pair { T x, y; };
 static inline void b200_cp_commit() {}
 template <int N> static inline void b200_cp_wait() {}
 static double emu_tmem[1024][256];
