@@ -373,9 +373,10 @@ _CASES += [("vertical_advection_dycore", (9, 5, 80)), ("vertical_advection_dycor
 
 @pytest.mark.parametrize("name,domain,knobs", [
     ("fv3_chain", (130, 37, 2), {"B200_MARCH_STRIP": "8"}),                              # 5 warps x 5 strips
-    ("fv3_chain", (130, 21, 3), {"B200_MARCH_STRIP": "5", "B200_MARCH_COLUMNS": "2"}),   # two columns per lane
+    ("fv3_chain", (130, 21, 3), {"B200_MARCH_STRIP": "5", "B200_MARCH_COLUMNS": "1", "B200_MARCH_WARPS": "4"}),   # one column per lane
     ("fv3_chain", (61, 19, 2), {"B200_MARCH_STRIP": "16", "B200_MARCH_LEAD": "1", "B200_MARCH_WARPS": "1"}),
-    ("horizontal_diffusion__tile", (120, 40, 2), {"B200_MARCH_STRIP": "8", "B200_MARCH_COLUMNS": "2"}),
+    ("horizontal_diffusion__tile", (120, 40, 2), {"B200_MARCH_STRIP": "8", "B200_MARCH_COLUMNS": "1"}),
+    ("horizontal_diffusion__tile", (121, 40, 2), {"B200_MARCH_STRIP": "8", "B200_MARCH_PAIRS": "0"}),  # a ring per column
     ("exec_info_diffusion", (59, 33, 3), {"B200_MARCH_STRIP": "4", "B200_MARCH_LEAD": "7"}),
     ("simple_horizontal_diffusion__tile", (63, 30, 2), {"B200_MARCH_STRIP": "8"}),
     ("native_functions__tile", (40, 13, 2), {"B200_MARCH_STRIP": "8", "B200_MARCH": "force"}),      # two stages: forced
@@ -384,7 +385,8 @@ _CASES += [("vertical_advection_dycore", (9, 5, 80)), ("vertical_advection_dycor
 ])
 def test_warp_march_kernels_over_strips_and_knobs(name, domain, knobs, monkeypatch):
     """The warp-march form (lowering_march.py) with short strips (several strips per column block, prologue rows of one
-    strip overlapping the previous one), one and two columns per lane, other prefetch distances: bit-exact against the
+    strip overlapping the previous one), one and two columns per lane (paired ring elements or a ring per column),
+    other prefetch distances: bit-exact against the
     reference's numpy backend on the host-emulated kernels."""
     for k, v in knobs.items():
         monkeypatch.setenv(k, v)

@@ -176,6 +176,36 @@ def test_fv3_chain_at_baseline_config_3():
     assert 0.05 < (want == 0).mean() < 0.95
 
 
+@pytest.mark.parametrize("aligned_at", [(3, 3, 0), (0, 0, 0), (2, 3, 0)])
+def test_warp_march_column_pairs_whatever_the_alignment(aligned_at):
+    """Two columns per lane are one 16-byte ring element where the pair is aligned in global memory (origin on a
+    16-byte boundary: the gt4py default, aligned_index = origin) and two 8-byte copies otherwise (origin 3 elements
+    past the boundary; one field of each kind in the third case).  A domain that is not a multiple of the warp's 56
+    result columns, so the last warp is moved west onto an odd or even column as well."""
+    from gt4py_b200 import generated, storage
+    from oracle import chain
+    from oracle import inputs as gen
+
+    if EMU:
+        from tests import emu_abi
+
+        emu_abi.activate()
+    dom, h = ((130, 21, 3) if EMU else (333, 77, 5)), chain.HALO
+    st = generated.load_plan(os.path.join(GEN, "fv3_chain"))
+    assert st._plan_["kernels"][0]["kind"] == "march" and st._plan_["kernels"][0]["columns_per_lane"] == 2
+    f = {}
+    for n, (name, seed) in enumerate((("phi", 91), ("u", 92), ("v", 93))):
+        at = aligned_at if aligned_at != (2, 3, 0) else ((3, 3, 0), (0, 0, 0), (2, 3, 0))[n]
+        f[name] = storage.empty((dom[0] + 2 * h, dom[1] + 2 * h, dom[2]), aligned_index=at)
+        storage.fill_synthetic(f[name], seed, -1.0, 1.5, global_offset=(-h, -h))
+    out = storage.zeros(dom)
+    st(f["phi"], f["u"], f["v"], out, dt=0.05, alpha=0.03, origin={"_all_": (h, h, 0), "out": (0, 0, 0)}, domain=dom)
+    host = {name: gen.hashed_window(-h, -h, dom[0] + 2 * h, dom[1] + 2 * h, dom[2], seed, -1.0, 1.5)
+            for name, seed in (("phi", 91), ("u", 92), ("v", 93))}
+    want = chain.fv3_chain(host["phi"], host["u"], host["v"], 0.05, 0.03)
+    assert np.array_equal(out.asnumpy(), want)
+
+
 def test_index_width_switch_beyond_two_to_the_31():
     """A field whose element span exceeds 2^31 - 2^20 must take the 64-bit entry points (`<k>`, not `<k>_u`) and
     still be right: ONE input is a K-strided view of a 17.7 GB allocation (little data, huge span)."""
