@@ -176,6 +176,31 @@ def test_fv3_chain_at_baseline_config_3():
     assert 0.05 < (want == 0).mean() < 0.95
 
 
+@pytest.mark.parametrize("ni", [1, 2, 55, 56, 57, 111, 112, 113, 169])
+def test_warp_march_column_pairs_around_the_warp_width(ni):
+    """Domains one column short of / at / past a multiple of the 56 result columns of a warp (two columns per lane):
+    the warp moved west, lanes whose pair is cut by the domain's edge, a single column."""
+    from gt4py_b200 import generated, storage
+    from oracle import chain
+    from oracle import inputs as gen
+
+    if EMU:
+        from tests import emu_abi
+
+        emu_abi.activate()
+    dom, h = (ni, 9 if EMU else 70, 2), chain.HALO
+    st = generated.load_plan(os.path.join(GEN, "fv3_chain"))
+    f = {}
+    for name, seed in (("phi", 31), ("u", 32), ("v", 33)):
+        f[name] = storage.empty((dom[0] + 2 * h, dom[1] + 2 * h, dom[2]), aligned_index=(h, h, 0))
+        storage.fill_synthetic(f[name], seed, -1.0, 1.5, global_offset=(-h, -h))
+    out = storage.zeros(dom)
+    st(f["phi"], f["u"], f["v"], out, dt=0.05, alpha=0.03, origin={"_all_": (h, h, 0), "out": (0, 0, 0)}, domain=dom)
+    host = {name: gen.hashed_window(-h, -h, dom[0] + 2 * h, dom[1] + 2 * h, dom[2], seed, -1.0, 1.5)
+            for name, seed in (("phi", 31), ("u", 32), ("v", 33))}
+    assert np.array_equal(out.asnumpy(), chain.fv3_chain(host["phi"], host["u"], host["v"], 0.05, 0.03))
+
+
 @pytest.mark.parametrize("aligned_at", [(3, 3, 0), (0, 0, 0), (2, 3, 0)])
 def test_warp_march_column_pairs_whatever_the_alignment(aligned_at):
     """Two columns per lane are one 16-byte ring element where the pair is aligned in global memory (origin on a
