@@ -393,6 +393,30 @@ def test_warp_march_kernels_over_strips_and_knobs(name, domain, knobs, monkeypat
     test_lowering_against_the_reference_at_other_sizes(name, domain, rebuild=True, expect_kind="march")
 
 
+def test_tma_fed_column_kernel_has_a_producer_row_and_compiles(monkeypatch):
+    """The `<k>_t` entry of the fused column template (lowering_colfuse.TMA_RINGS, off by default): one more row of
+    threads than the consumers' block, whose first lane issues the CTA's whole level stream; the plan says so, the
+    host emulation leaves the entry out, and nvcc accepts it for sm_100a.  (Values: tests/test_large_sizes_gpu.py.)"""
+    _gt4py()
+    sys.path.insert(0, os.path.join(os.path.dirname(HERE), "tools"))
+    import make_generated_fixtures as mk
+    from gt4py.cartesian import gtscript
+
+    from gt4py_b200 import lowering_colfuse
+
+    monkeypatch.setattr(lowering_colfuse, "TMA_RINGS", True)
+    fn, ext = mk.definitions()["vertical_advection_dycore"][:2]
+    st = gtscript.stencil("b200", fn, externals=ext, rebuild=True, name="vadv_tma_cpu", use_library_kernels=False)
+    impl = type(st)._b200()
+    (k,) = impl._plan_["kernels"]
+    assert k["kind"] == "colfuse" and k["tma"]["producer_rows"] == 1
+    bx, by = k["block"]
+    src = open(os.path.join(impl._dir_, "kernel.cu")).read()
+    assert f"__launch_bounds__({bx * (by + 1)}, 1) {k['name']}_t(" in src
+    assert f"if (tid == {bx * by}) {{" in src and "b200_tma_load_3d(" in src
+    assert os.path.getsize(generated.compile_cubin(os.path.join(impl._dir_, "kernel.cu"))) > 0
+
+
 @pytest.mark.parametrize("name,domain", [("vertical_advection_dycore", (300, 7, 66)), ("tridiagonal_solver", (260, 5, 70)),
                                          ("column_physics", (131, 6, 9)), ("vertical_advection_dycore__f32", (40, 3, 90))])
 def test_pipelined_column_kernels(name, domain, monkeypatch):
