@@ -161,7 +161,10 @@ def emit(kname: str, unit, block_ext, fields, field_ext, scalar_names, locals_, 
     IHI = max([e[1] for e in s_ext] + [e[1] for e in in_ext.values()])
     ILOa = -((-ILO + C - 1) // C * C)                  # first column of lane 0, relative to the warp's first result
     WO = 32 * C - (IHI - ILOa)                          # result columns per warp
-    if C == 2 and _knob("B200_MARCH_PAIRS", 1):
+    # two columns per lane: the pair is ONE ring element (16 / 8 bytes: one cp.async and one LDS.128 / LDS.64 per row
+    # where the pair is whole and aligned in global memory, two plain copies into the same element otherwise)
+    PAIR = C == 2 and bool(_knob("B200_MARCH_PAIRS", 1))
+    if PAIR:
         WO -= WO % 2                                    # (every warp's first column even: its lanes' pairs stay aligned)
     if WO < 8 * C:
         return None
@@ -179,9 +182,6 @@ def emit(kname: str, unit, block_ext, fields, field_ext, scalar_names, locals_, 
     if STATIC:
         U = max(U, RD)
         NIT = (NIT + U - 1) // U * U
-    # two columns per lane: the pair is ONE ring element (16 / 8 bytes: one cp.async and one LDS.128 / LDS.64 per row
-    # where the pair is whole and aligned in global memory, two plain copies into the same element otherwise)
-    PAIR = C == 2 and bool(_knob("B200_MARCH_PAIRS", 1))
     ring_off: Dict[Tuple[str, int], int] = {}
     smem_bytes = 0
     for name in inputs:
@@ -407,7 +407,7 @@ def emit(kname: str, unit, block_ext, fields, field_ext, scalar_names, locals_, 
         S += ["    " + ln for ln in loop(False)]
         S.append("    }")
     all_exts = list(exts.values())
-    meta = {"name": kname, "kind": "march", "columns_per_lane": C, "strip": STRIP, "warps": WARPS, "result_columns": WO,
+    meta = {"name": kname, "kind": "march", "columns_per_lane": C, "paired_ring_elements": bool(PAIR), "strip": STRIP, "warps": WARPS, "result_columns": WO,
             "stages": len(stages), "lags": lag, "period": U, "lead": LEAD, "ring_rows": RD,
             "smem_bytes": int(smem_bytes), "input_rings": inputs,
             "register_windows": {n: depth[n] for n in windows}, "register_temporaries": sorted(regs),
